@@ -1,0 +1,148 @@
+/*
+ * eegspec.h -- C ABI of the B200-native EEG -> spectrogram transform (libeegspec.so).
+ *
+ * Plain C: pointers, sizes, POD structs; no torch / C++ types cross this boundary.
+ * Every entry point returns an int status: 0 = ok, negative = argument error (EEGSPEC_E*),
+ * positive = a cudaError_t raised by the launch.  Nothing throws across the ABI.  All device
+ * entry points are asynchronous on the CUDA stream that is passed in (a cudaStream_t cast to
+ * void*; NULL = the legacy default stream) and never synchronise.  The library is stateless
+ * apart from per-device constant tables for the mel transform that are built once, under a lock.
+ *
+ * The reference (KC-decoder/Multimodal-Brain-Pattern-Identification_XAI) is pure Python and
+ * defines no FFI of its own; each entry point below names the reference code it replaces.
+ */
+#ifndef EEGSPEC_H_
+#define EEGSPEC_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define EEGSPEC_ABI_VERSION 1
+
+enum {
+  EEGSPEC_OK = 0,
+  EEGSPEC_EINVAL = -1,        /* null pointer, non-positive size, bad stride                  */
+  EEGSPEC_ENOVERLAP = -2,     /* noverlap >= nperseg (SciPy: "noverlap must be less than ...") */
+  EEGSPEC_EUNSUPPORTED = -3,  /* legal for the reference, not implemented here (no fallback)   */
+  EEGSPEC_ESHORT = -4,        /* record shorter than one window / the crop length              */
+  EEGSPEC_EWORKSPACE = -5,    /* workspace missing or too small                                */
+  EEGSPEC_EALIGN = -6         /* output pointer / row pitch not 16-byte aligned                */
+};
+
+int eegspec_abi_version(void);
+/* Static string for a status returned by any function below (cudaGetErrorString for > 0). */
+const char *eegspec_strerror(int status);
+
+/* ------------------------------------------------------------------------------------------
+ * Mode R: the reference's compute_stft(signal, config)
+ *   /root/reference/root/src/utils/DiffEEG_utils.py:27-76  (called from
+ *   /root/reference/root/src/training/DiffEEG_train.py:131,209)
+ * A "row" is one (record, channel) series; rows = B*C.
+ * ------------------------------------------------------------------------------------------ */
+
+/* Integer framing facts of scipy.signal.stft(boundary='zeros', padded=True) as used at
+ * DiffEEG_utils.py:46-51 -- what the reference gets implicitly from SciPy.  Host only. */
+typedef struct eegspec_stft_plan {
+  int32_t hop;            /* nperseg - noverlap                                         */
+  int32_t half;           /* nperseg / 2 zeros prepended and appended                   */
+  int32_t nadd;           /* extra zeros appended to reach a whole number of hops       */
+  int32_t n_freqs;        /* nperseg / 2 + 1                                            */
+  int64_t n_frames;       /* STFT columns                                               */
+  int64_t n_slots;        /* frames the kernel actually evaluates (<= n_frames)         */
+  int32_t gather;         /* 1: only the frames bracketing an output column are evaluated */
+  int32_t reserved;
+} eegspec_stft_plan;
+
+int eegspec_stft_plan_make(int64_t length, int nperseg, int noverlap, int64_t out_cols,
+                           eegspec_stft_plan *plan);
+
+/* Left knot index np.interp uses for output column j (DiffEEG_utils.py:57-61). Host only. */
+int64_t eegspec_interp_bracket(int64_t j, int64_t n_frames, int64_t out_cols);
+
+/* Scratch bytes eegspec_stft_image_f32 needs for this shape (0 when everything fits on chip). */
+size_t eegspec_stft_image_workspace(int64_t rows, int64_t length, int nperseg, int noverlap,
+                                    int64_t out_cols);
+
+/* x: device, rows series of `length` fp32, consecutive rows `row_stride` elements apart.
+ * out: device, (rows, nperseg/2+1, out_cols) fp32 contiguous, 16-byte aligned.
+ * Replaces DiffEEG_utils.py:43-74 for all rows at once: STFT -> log1p|Z| -> linear
+ * resample to out_cols (2000 in the reference) -> per-(row,freq) min-max with eps (1e-8). */
+int eegspec_stft_image_f32(const float *x, int64_t rows, int64_t length, int64_t row_stride,
+                           int nperseg, int noverlap, int64_t out_cols, float eps, float *out,
+                           void *workspace, size_t workspace_bytes, void *stream);
+
+/* The plotting twin compute_stft_single (DiffEEG_utils.py:504-509): log1p|Z| only.
+ * out: device, (rows, nperseg/2+1, n_frames) fp32 contiguous. */
+int eegspec_stft_logmag_f32(const float *x, int64_t rows, int64_t length, int64_t row_stride,
+                            int nperseg, int noverlap, float *out, void *stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Mode N: montage differences -> NaN fill -> Hann/STFT -> mel -> dB -> (x+40)/40 -> chain mean
+ *   front half replaces /root/reference/root/config/config.yml:529-545 (pair list),
+ *   /root/reference/root/src/utils/data_utils.py:183-215 (differencing),
+ *   /root/reference/root/src/utils/cfg_utils.py:369-371 (crop), :380-385 (NaN fill);
+ *   back half (mel / dB) is specified by BASELINE.json only -- see DESIGN.md.
+ * ------------------------------------------------------------------------------------------ */
+#define EEGSPEC_MAX_PAIRS 32
+
+typedef struct eegspec_mel_params {
+  int32_t sr;            /* 200                                                          */
+  int32_t n_fft;         /* 1024                                                         */
+  int32_t win_length;    /* 128                                                          */
+  int32_t hop;           /* 0 => crop / n_time_div (10000 // 256 = 39)                   */
+  int32_t n_mels;        /* 128                                                          */
+  float fmin;            /* 0                                                            */
+  float fmax;            /* 20                                                           */
+  int32_t crop;          /* 10000: middle window, offset (L - crop)//2                   */
+  int32_t n_time_div;    /* 256: hop = crop // n_time_div; width = (n_frames//32)*32     */
+  float amin;            /* 1e-10                                                        */
+  float top_db;          /* 80                                                           */
+  float db_offset;       /* 40                                                           */
+  float db_scale;        /* 40                                                           */
+  int32_t pad_mode;      /* 0 = constant zeros (librosa >= 0.10), 1 = reflect (< 0.10)   */
+  int32_t n_chains;      /* 4                                                            */
+  int32_t pairs_per_chain; /* 4                                                          */
+  int32_t pair_a[EEGSPEC_MAX_PAIRS]; /* channel index of the minuend, chain-major        */
+  int32_t pair_b[EEGSPEC_MAX_PAIRS]; /* channel index of the subtrahend                  */
+  int32_t time_major;    /* 0: record is (n_ch, L) channel-major; 1: (L, n_ch)           */
+  int32_t engine;        /* 0 = default for this build, 1 = fp32 SIMT, 2 = tcgen05 split-fp16 */
+} eegspec_mel_params;
+
+/* Fills the defaults above (HMS montage LL, LP, RP, RR in EEG_COLUMNS order). */
+void eegspec_mel_params_default(eegspec_mel_params *p);
+
+/* Output geometry for these parameters: frames per pair and kept time columns. */
+int eegspec_melspec_geometry(const eegspec_mel_params *p, int32_t *n_frames, int32_t *n_time);
+
+size_t eegspec_melspec_workspace(int64_t batch, const eegspec_mel_params *p);
+
+/* eeg: device fp32, `batch` records `rec_stride` elements apart, each n_ch x length
+ * (or length x n_ch when time_major).  out: device (batch, n_mels, n_time, n_chains) fp32. */
+int eegspec_melspec_f32(const float *eeg, int64_t batch, int32_t n_ch, int64_t length,
+                        int64_t rec_stride, const eegspec_mel_params *p, float *out,
+                        void *workspace, size_t workspace_bytes, void *stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Host-buffer front doors (what the reference's caller has: CPU tensors from a DataLoader).
+ * x / out are HOST pointers (pinned for full PCIe speed; pageable works, slower).  The call
+ * streams record chunks through device buffers on `device` (H2D, kernels, D2H overlapped on
+ * internal streams) and returns after the last byte of `out` has landed.
+ * ------------------------------------------------------------------------------------------ */
+int eegspec_stft_image_host_f32(const float *x, int64_t rows, int64_t length, int nperseg,
+                                int noverlap, int64_t out_cols, float eps, float *out,
+                                int device);
+
+int eegspec_melspec_host_f32(const float *eeg, int64_t batch, int32_t n_ch, int64_t length,
+                             const eegspec_mel_params *p, float *out, int device);
+
+/* Number of kernel launches issued by this library since load (bench bookkeeping). */
+int64_t eegspec_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* EEGSPEC_H_ */

@@ -1,0 +1,247 @@
+// extern "C" surface of libeegspec.so (declared in include/eegspec.h).
+#include <atomic>
+#include <mutex>
+
+#include "internal.h"
+
+namespace eegspec {
+
+static std::atomic<long long> g_launches{0};
+void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+
+// Montage of the north_star, as channel indices into EEG_COLUMNS
+// (/root/reference/root/config/config.yml:34-54) for the first 16 map_features pairs
+// (/root/reference/root/config/config.yml:529-545): chains LL, LP, RP, RR.
+//   Fp1=0 F3=1 C3=2 P3=3 F7=4 T3=5 T5=6 O1=7 Fz=8 Cz=9 Pz=10 Fp2=11 F4=12 C4=13 P4=14 F8=15
+//   T4=16 T6=17 O2=18 EKG=19
+static const int kPairA[16] = {0, 4, 5, 6, 0, 1, 2, 3, 11, 15, 16, 17, 11, 12, 13, 14};
+static const int kPairB[16] = {4, 5, 6, 7, 1, 2, 3, 7, 15, 16, 17, 18, 12, 13, 14, 18};
+
+// ---- host-buffer pipeline -------------------------------------------------------------------
+constexpr int kPipeDepth = 3;
+struct HostPipe {
+  bool ready = false;
+  cudaStream_t stream[kPipeDepth] = {};
+  void* buf[kPipeDepth][3] = {};   // in, out, workspace
+  size_t cap[kPipeDepth][3] = {};
+};
+static std::mutex g_pipe_mu;
+static HostPipe g_pipes[64];
+
+static cudaError_t pipe_reserve(HostPipe& p, int slot, int which, size_t bytes) {
+  if (bytes <= p.cap[slot][which]) return cudaSuccess;
+  if (p.buf[slot][which]) {
+    cudaError_t e = cudaFree(p.buf[slot][which]);
+    if (e != cudaSuccess) return e;
+    p.buf[slot][which] = nullptr;
+    p.cap[slot][which] = 0;
+  }
+  cudaError_t e = cudaMalloc(&p.buf[slot][which], bytes);
+  if (e == cudaSuccess) p.cap[slot][which] = bytes;
+  return e;
+}
+
+static int pipe_open(int device, HostPipe** out) {
+  if (device < 0 || device >= 64) return EEGSPEC_EINVAL;
+  cudaError_t e = cudaSetDevice(device);
+  if (e != cudaSuccess) return (int)e;
+  HostPipe& p = g_pipes[device];
+  if (!p.ready) {
+    for (int i = 0; i < kPipeDepth; ++i) {
+      e = cudaStreamCreateWithFlags(&p.stream[i], cudaStreamNonBlocking);
+      if (e != cudaSuccess) return (int)e;
+    }
+    p.ready = true;
+  }
+  *out = &p;
+  return EEGSPEC_OK;
+}
+
+}  // namespace eegspec
+
+using namespace eegspec;
+
+extern "C" {
+
+int eegspec_abi_version(void) { return EEGSPEC_ABI_VERSION; }
+
+const char* eegspec_strerror(int status) {
+  switch (status) {
+    case EEGSPEC_OK: return "ok";
+    case EEGSPEC_EINVAL: return "invalid argument (null pointer, non-positive size or bad stride)";
+    case EEGSPEC_ENOVERLAP: return "noverlap must be less than nperseg.";
+    case EEGSPEC_EUNSUPPORTED: return "parameter combination not implemented by the CUDA path (no fallback exists)";
+    case EEGSPEC_ESHORT: return "record shorter than one window / the crop length";
+    case EEGSPEC_EWORKSPACE: return "workspace missing or too small";
+    case EEGSPEC_EALIGN: return "pointer not 16-byte aligned";
+    default: break;
+  }
+  if (status > 0) return cudaGetErrorString(static_cast<cudaError_t>(status));
+  return "unknown eegspec status";
+}
+
+int eegspec_stft_plan_make(int64_t length, int nperseg, int noverlap, int64_t out_cols,
+                           eegspec_stft_plan* plan) {
+  return stft_plan_make(length, nperseg, noverlap, out_cols, plan);
+}
+
+int64_t eegspec_interp_bracket(int64_t j, int64_t n_frames, int64_t out_cols) {
+  return interp_bracket(j, n_frames, out_cols);
+}
+
+size_t eegspec_stft_image_workspace(int64_t rows, int64_t length, int nperseg, int noverlap,
+                                    int64_t out_cols) {
+  return stft_image_workspace(rows, length, nperseg, noverlap, out_cols);
+}
+
+int eegspec_stft_image_f32(const float* x, int64_t rows, int64_t length, int64_t row_stride,
+                           int nperseg, int noverlap, int64_t out_cols, float eps, float* out,
+                           void* workspace, size_t workspace_bytes, void* stream) {
+  return stft_image_launch(x, rows, length, row_stride, nperseg, noverlap, out_cols, eps, out,
+                           workspace, workspace_bytes, static_cast<cudaStream_t>(stream));
+}
+
+int eegspec_stft_logmag_f32(const float* x, int64_t rows, int64_t length, int64_t row_stride,
+                            int nperseg, int noverlap, float* out, void* stream) {
+  return stft_logmag_launch(x, rows, length, row_stride, nperseg, noverlap, out,
+                            static_cast<cudaStream_t>(stream));
+}
+
+void eegspec_mel_params_default(eegspec_mel_params* p) {
+  if (!p) return;
+  *p = eegspec_mel_params{};
+  p->sr = 200;
+  p->n_fft = 1024;
+  p->win_length = 128;
+  p->hop = 0;
+  p->n_mels = 128;
+  p->fmin = 0.f;
+  p->fmax = 20.f;
+  p->crop = 10000;
+  p->n_time_div = 256;
+  p->amin = 1e-10f;
+  p->top_db = 80.f;
+  p->db_offset = 40.f;
+  p->db_scale = 40.f;
+  p->pad_mode = 0;
+  p->n_chains = 4;
+  p->pairs_per_chain = 4;
+  for (int i = 0; i < 16; ++i) {
+    p->pair_a[i] = kPairA[i];
+    p->pair_b[i] = kPairB[i];
+  }
+  p->time_major = 0;
+  p->engine = 0;
+}
+
+int eegspec_melspec_geometry(const eegspec_mel_params* p, int32_t* n_frames, int32_t* n_time) {
+  MelGeometry g;
+  const int rc = melspec_geometry(p, &g);
+  if (rc != EEGSPEC_OK) return rc;
+  if (n_frames) *n_frames = g.n_frames;
+  if (n_time) *n_time = g.n_time;
+  return EEGSPEC_OK;
+}
+
+size_t eegspec_melspec_workspace(int64_t batch, const eegspec_mel_params* p) {
+  return melspec_workspace(batch, p);
+}
+
+int eegspec_melspec_f32(const float* eeg, int64_t batch, int32_t n_ch, int64_t length,
+                        int64_t rec_stride, const eegspec_mel_params* p, float* out,
+                        void* workspace, size_t workspace_bytes, void* stream) {
+  return melspec_launch(eeg, batch, n_ch, length, rec_stride, p, out, workspace, workspace_bytes,
+                        static_cast<cudaStream_t>(stream));
+}
+
+int eegspec_stft_image_host_f32(const float* x, int64_t rows, int64_t length, int nperseg,
+                                int noverlap, int64_t out_cols, float eps, float* out,
+                                int device) {
+  if (!x || !out || rows <= 0 || length <= 0) return EEGSPEC_EINVAL;
+  eegspec_stft_plan pl;
+  int rc = stft_plan_make(length, nperseg, noverlap, out_cols, &pl);
+  if (rc != EEGSPEC_OK) return rc;
+  std::lock_guard<std::mutex> lock(g_pipe_mu);
+  HostPipe* pipe = nullptr;
+  if ((rc = pipe_open(device, &pipe)) != EEGSPEC_OK) return rc;
+
+  const size_t in_row = (size_t)length * sizeof(float);
+  const size_t out_row = (size_t)pl.n_freqs * out_cols * sizeof(float);
+  // ~128 MiB of image per chunk keeps three chunks in flight without hogging HBM.
+  int64_t chunk = (int64_t)((128ull << 20) / out_row);
+  if (chunk < 1) chunk = 1;
+  if (chunk > rows) chunk = rows;
+  const size_t ws_bytes = stft_image_workspace(chunk, length, nperseg, noverlap, out_cols);
+
+  int n = 0;
+  for (int64_t r0 = 0; r0 < rows; r0 += chunk, ++n) {
+    const int s = n % kPipeDepth;
+    const int64_t nr = rows - r0 < chunk ? rows - r0 : chunk;
+    cudaError_t e;
+    if ((e = pipe_reserve(*pipe, s, 0, in_row * chunk)) != cudaSuccess) return (int)e;
+    if ((e = pipe_reserve(*pipe, s, 1, out_row * chunk)) != cudaSuccess) return (int)e;
+    if (ws_bytes && (e = pipe_reserve(*pipe, s, 2, ws_bytes)) != cudaSuccess) return (int)e;
+    cudaStream_t st = pipe->stream[s];
+    e = cudaMemcpyAsync(pipe->buf[s][0], x + r0 * length, in_row * nr, cudaMemcpyHostToDevice, st);
+    if (e != cudaSuccess) return (int)e;
+    rc = stft_image_launch(static_cast<const float*>(pipe->buf[s][0]), nr, length, length, nperseg,
+                           noverlap, out_cols, eps, static_cast<float*>(pipe->buf[s][1]),
+                           pipe->buf[s][2], pipe->cap[s][2], st);
+    if (rc != EEGSPEC_OK) return rc;
+    e = cudaMemcpyAsync(out + r0 * (int64_t)pl.n_freqs * out_cols, pipe->buf[s][1], out_row * nr,
+                        cudaMemcpyDeviceToHost, st);
+    if (e != cudaSuccess) return (int)e;
+  }
+  for (int s = 0; s < kPipeDepth; ++s) {
+    cudaError_t e = cudaStreamSynchronize(pipe->stream[s]);
+    if (e != cudaSuccess) return (int)e;
+  }
+  return EEGSPEC_OK;
+}
+
+int eegspec_melspec_host_f32(const float* eeg, int64_t batch, int32_t n_ch, int64_t length,
+                             const eegspec_mel_params* p, float* out, int device) {
+  if (!eeg || !out || batch <= 0 || n_ch <= 0 || length <= 0) return EEGSPEC_EINVAL;
+  MelGeometry g;
+  int rc = melspec_geometry(p, &g);
+  if (rc != EEGSPEC_OK) return rc;
+  std::lock_guard<std::mutex> lock(g_pipe_mu);
+  HostPipe* pipe = nullptr;
+  if ((rc = pipe_open(device, &pipe)) != EEGSPEC_OK) return rc;
+
+  const size_t in_rec = (size_t)n_ch * length * sizeof(float);
+  const size_t out_rec = (size_t)p->n_mels * g.n_time * p->n_chains * sizeof(float);
+  int64_t chunk = 64;
+  if (chunk > batch) chunk = batch;
+  const size_t ws_bytes = melspec_workspace(chunk, p);
+
+  int n = 0;
+  for (int64_t r0 = 0; r0 < batch; r0 += chunk, ++n) {
+    const int s = n % kPipeDepth;
+    const int64_t nb = batch - r0 < chunk ? batch - r0 : chunk;
+    cudaError_t e;
+    if ((e = pipe_reserve(*pipe, s, 0, in_rec * chunk)) != cudaSuccess) return (int)e;
+    if ((e = pipe_reserve(*pipe, s, 1, out_rec * chunk)) != cudaSuccess) return (int)e;
+    if ((e = pipe_reserve(*pipe, s, 2, ws_bytes)) != cudaSuccess) return (int)e;
+    cudaStream_t st = pipe->stream[s];
+    e = cudaMemcpyAsync(pipe->buf[s][0], eeg + r0 * (int64_t)n_ch * length, in_rec * nb,
+                        cudaMemcpyHostToDevice, st);
+    if (e != cudaSuccess) return (int)e;
+    rc = melspec_launch(static_cast<const float*>(pipe->buf[s][0]), nb, n_ch, length,
+                        (long long)n_ch * length, p, static_cast<float*>(pipe->buf[s][1]),
+                        pipe->buf[s][2], pipe->cap[s][2], st);
+    if (rc != EEGSPEC_OK) return rc;
+    e = cudaMemcpyAsync(out + r0 * (int64_t)(out_rec / sizeof(float)), pipe->buf[s][1],
+                        out_rec * nb, cudaMemcpyDeviceToHost, st);
+    if (e != cudaSuccess) return (int)e;
+  }
+  for (int s = 0; s < kPipeDepth; ++s) {
+    cudaError_t e = cudaStreamSynchronize(pipe->stream[s]);
+    if (e != cudaSuccess) return (int)e;
+  }
+  return EEGSPEC_OK;
+}
+
+int64_t eegspec_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
+
+}  // extern "C"

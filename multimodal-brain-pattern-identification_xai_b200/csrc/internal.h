@@ -1,0 +1,36 @@
+// Internal C++ interface between the kernel translation units and the C ABI (abi.cu).
+#pragma once
+#include <cuda_runtime.h>
+#include <stddef.h>
+#include <stdint.h>
+
+#include "../../include/eegspec.h"
+
+namespace eegspec {
+
+void count_launch();
+
+// stft_image.cu
+int stft_plan_make(long long length, int nperseg, int noverlap, long long out_cols,
+                   eegspec_stft_plan* plan);
+long long interp_bracket(long long j, long long n_frames, long long out_cols);
+size_t stft_image_workspace(long long rows, long long length, int nperseg, int noverlap,
+                            long long out_cols);
+int stft_image_launch(const float* x, long long rows, long long length, long long row_stride,
+                      int nperseg, int noverlap, long long out_cols, float eps, float* out,
+                      void* workspace, size_t workspace_bytes, cudaStream_t st);
+int stft_logmag_launch(const float* x, long long rows, long long length, long long row_stride,
+                       int nperseg, int noverlap, float* out, cudaStream_t st);
+
+// melspec.cu
+struct MelGeometry {
+  int hop, n_frames, n_time, n_pairs;
+  int k_lo, k_hi;  // inclusive range of rFFT bins with a non-zero mel weight
+};
+int melspec_geometry(const eegspec_mel_params* p, MelGeometry* g);
+size_t melspec_workspace(long long batch, const eegspec_mel_params* p);
+int melspec_launch(const float* eeg, long long batch, int n_ch, long long length,
+                   long long rec_stride, const eegspec_mel_params* p, float* out, void* workspace,
+                   size_t workspace_bytes, cudaStream_t st);
+
+}  // namespace eegspec

@@ -1,0 +1,562 @@
+// Mode N: bipolar montage -> NaN fill -> Hann STFT power -> mel -> dB -> (x+40)/40 -> chain mean.
+//
+// Front half follows the reference (pair list /root/reference/root/config/config.yml:529-545,
+// differencing /root/reference/root/src/utils/data_utils.py:183-215, middle crop
+// /root/reference/root/src/utils/cfg_utils.py:369-371, NaN fill cfg_utils.py:380-385); the mel/dB
+// back half is the librosa recipe BASELINE.json names (see oracle/melspec_oracle.py).
+//
+// Engine 1 (this file): exact fp32 SIMT.
+//   The 128-sample Hann window sits in a 1024-point frame and the mel bank (0..20 Hz) only
+//   touches rFFT bins 1..102, so the transform is a pruned DFT, not an FFT: fold the symmetric
+//   window about its centre (even part E[m], odd part O[m], m < 64) and the frame spectrum is
+//   two small real matrix products  Re = E . cos, Im = -O . sin  with a constant
+//   64 x 104 table pair.  |X|^2 is independent of where the window sits in the frame.
+//   kernel 1  one CTA per (record, pair): difference + NaN fill into shared memory, then two
+//             tiles of 128 frames: build E/O, register-tiled FFMA product (4 frames x 13 bins x
+//             {cos,sin} per thread), power, 2-tap sparse mel, 10 log10 -> scratch; pair maximum.
+//   kernel 2  dB referencing (needs the pair maximum), top_db clip, (x+40)/40, mean over the
+//             pairs of a chain, one float4 (4 chains) per (mel, time) pixel.
+#include <math.h>
+
+#include <mutex>
+#include <vector>
+
+#include "common.cuh"
+#include "internal.h"
+
+namespace eegspec {
+
+constexpr int kFold = 64;       // win_length / 2
+constexpr int kBinGroups = 8;   // one warp per bin group
+constexpr int kBinsPerGroup = 13;
+constexpr int kBinSlots = kBinGroups * kBinsPerGroup;  // 104 >= bins with mel weight
+constexpr int kGroupPitch = 16;                        // table row pitch per group (float4 x 4)
+constexpr int kTileFrames = 128;
+constexpr int kMelThreads = 256;
+constexpr int kMaxMels = 256;
+constexpr int kMaxCrop = 12288;
+
+struct MelTables {            // device-resident constant tables for one parameter set
+  float* cos_t;               // [kFold][kBinGroups][kGroupPitch]
+  float* sin_t;
+  float* win_half;            // [kFold]  w[W/2 + m]
+  int* mel_k0;                // [n_mels] first tap, as a bin slot (bin - k_lo)
+  float* mel_w0;              // [n_mels]
+  float* mel_w1;              // [n_mels]
+};
+
+struct MelArgs {
+  const float* eeg;
+  float* q;       // [batch][pairs][n_mels][n_time]  10 log10(max(amin, mel))
+  float* refdb;   // [batch][pairs]                  10 log10(max(amin, max mel))
+  float* out;     // [batch][n_mels][n_time][n_chains]
+  MelTables t;
+  long long rec_stride, ch_stride, t_stride, length;
+  int crop, crop_off, hop, n_frames, n_time, n_mels, n_pairs, n_chains, ppc, pad_mode;
+  float amin, top_db, db_offset, inv_db_scale;
+  int pair_a[EEGSPEC_MAX_PAIRS], pair_b[EEGSPEC_MAX_PAIRS];
+};
+
+__device__ __forceinline__ float padded_sample(const float* y, int i, int n, int pad_mode) {
+  if (i < 0) {
+    if (pad_mode == 0) return 0.f;
+    i = -i;
+  } else if (i >= n) {
+    if (pad_mode == 0) return 0.f;
+    i = 2 * (n - 1) - i;
+  }
+  return (i >= 0 && i < n) ? y[i] : 0.f;
+}
+
+__global__ void __launch_bounds__(kMelThreads, 1) melspec_pair_kernel(const MelArgs a) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  float* cos_s = reinterpret_cast<float*>(smem_raw);              // kFold*128
+  float* sin_s = cos_s + kFold * kBinGroups * kGroupPitch;        // kFold*128
+  float* tile = sin_s + kFold * kBinGroups * kGroupPitch;         // E | O  (2*kFold*kTileFrames)
+  float* y = tile + 2 * kFold * kTileFrames;                      // crop
+  float* wh = y + ((a.crop + 3) & ~3);                            // kFold
+  float* mw0 = wh + kFold;                                        // n_mels
+  float* mw1 = mw0 + kMaxMels;
+  int* mk0 = reinterpret_cast<int*>(mw1 + kMaxMels);
+  __shared__ float red_a[kMelThreads / 32], red_b[kMelThreads / 32];
+  __shared__ float bcast[2];
+
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int pair = blockIdx.x;
+  const long long rec = blockIdx.y;
+  const float* ea = a.eeg + rec * a.rec_stride + a.pair_a[pair] * a.ch_stride + a.crop_off * a.t_stride;
+  const float* eb = a.eeg + rec * a.rec_stride + a.pair_b[pair] * a.ch_stride + a.crop_off * a.t_stride;
+
+  for (int i = tid; i < kFold * kBinGroups * kGroupPitch; i += kMelThreads) {
+    cos_s[i] = a.t.cos_t[i];
+    sin_s[i] = a.t.sin_t[i];
+  }
+  for (int i = tid; i < kFold; i += kMelThreads) wh[i] = a.t.win_half[i];
+  for (int i = tid; i < a.n_mels; i += kMelThreads) {
+    mw0[i] = a.t.mel_w0[i];
+    mw1[i] = a.t.mel_w1[i];
+    mk0[i] = a.t.mel_k0[i];
+  }
+
+  // Montage difference + NaN statistics (cfg_utils.py:380-385 applied to the difference).
+  float sum = 0.f, nans = 0.f;
+  for (int i = tid; i < a.crop; i += kMelThreads) {
+    const float d = __ldg(ea + i * a.t_stride) - __ldg(eb + i * a.t_stride);
+    y[i] = d;
+    if (d != d) nans += 1.f; else sum += d;
+  }
+  sum = warp_sum(sum);
+  nans = warp_sum(nans);
+  if (lane == 0) { red_a[warp] = sum; red_b[warp] = nans; }
+  __syncthreads();
+  if (warp == 0) {
+    float s = lane < kMelThreads / 32 ? red_a[lane] : 0.f;
+    float c = lane < kMelThreads / 32 ? red_b[lane] : 0.f;
+    s = warp_sum(s);
+    c = warp_sum(c);
+    if (lane == 0) { bcast[0] = s; bcast[1] = c; }
+  }
+  __syncthreads();
+  {
+    const float n_nan = bcast[1];
+    if (n_nan > 0.f) {
+      const bool all_nan = n_nan >= (float)a.crop;
+      const float fill = all_nan ? 0.f : bcast[0] / ((float)a.crop - n_nan);
+      for (int i = tid; i < a.crop; i += kMelThreads) {
+        const float d = y[i];
+        if (all_nan) y[i] = 0.f; else if (d != d) y[i] = fill;
+      }
+    }
+  }
+  __syncthreads();
+
+  float* E = tile;
+  float* O = tile + kFold * kTileFrames;
+  float* Pw = tile;  // [kBinSlots][kTileFrames], aliases E/O once the product is done
+  const int fg = lane, bg = warp;          // frames 4*fg.., bins 13*bg..
+  float vmax = 0.f;
+  float* qbase = a.q + ((rec * a.n_pairs + pair) * (long long)a.n_mels) * a.n_time;
+
+  const int n_tiles = (a.n_time + kTileFrames - 1) / kTileFrames;
+  for (int tl = 0; tl < n_tiles; ++tl) {
+    const int f0 = tl * kTileFrames;
+    // Fold the windowed frame about its centre sample f*hop.
+    for (int i = tid; i < kFold * kTileFrames; i += kMelThreads) {
+      const int m = i / kTileFrames, t = i % kTileFrames;
+      const int f = f0 + t;
+      float e = 0.f, o = 0.f;
+      if (f < a.n_frames) {
+        const int c = f * a.hop;
+        const float yp = padded_sample(y, c + m, a.crop, a.pad_mode);
+        if (m == 0) {
+          e = wh[0] * yp;
+        } else {
+          const float ym = padded_sample(y, c - m, a.crop, a.pad_mode);
+          e = wh[m] * (yp + ym);
+          o = wh[m] * (yp - ym);
+        }
+      }
+      E[i] = e;
+      O[i] = o;
+    }
+    __syncthreads();
+
+    float ac[4][kBinsPerGroup], as[4][kBinsPerGroup];
+#pragma unroll
+    for (int r = 0; r < 4; ++r)
+#pragma unroll
+      for (int k = 0; k < kBinsPerGroup; ++k) { ac[r][k] = 0.f; as[r][k] = 0.f; }
+
+#pragma unroll 2
+    for (int m = 0; m < kFold; ++m) {
+      const float4 e4 = *reinterpret_cast<const float4*>(E + m * kTileFrames + 4 * fg);
+      const float4 o4 = *reinterpret_cast<const float4*>(O + m * kTileFrames + 4 * fg);
+      const float ev[4] = {e4.x, e4.y, e4.z, e4.w}, ov[4] = {o4.x, o4.y, o4.z, o4.w};
+      float cv[kGroupPitch], sv[kGroupPitch];
+#pragma unroll
+      for (int v = 0; v < kGroupPitch / 4; ++v) {
+        const float4 c4 = *reinterpret_cast<const float4*>(cos_s + (m * kBinGroups + bg) * kGroupPitch + 4 * v);
+        const float4 s4 = *reinterpret_cast<const float4*>(sin_s + (m * kBinGroups + bg) * kGroupPitch + 4 * v);
+        cv[4 * v] = c4.x; cv[4 * v + 1] = c4.y; cv[4 * v + 2] = c4.z; cv[4 * v + 3] = c4.w;
+        sv[4 * v] = s4.x; sv[4 * v + 1] = s4.y; sv[4 * v + 2] = s4.z; sv[4 * v + 3] = s4.w;
+      }
+#pragma unroll
+      for (int r = 0; r < 4; ++r)
+#pragma unroll
+        for (int k = 0; k < kBinsPerGroup; ++k) {
+          ac[r][k] = fmaf(ev[r], cv[k], ac[r][k]);
+          as[r][k] = fmaf(ov[r], sv[k], as[r][k]);
+        }
+    }
+    __syncthreads();  // every warp is done reading E/O before Pw overwrites them
+
+#pragma unroll
+    for (int k = 0; k < kBinsPerGroup; ++k) {
+      float4 p;
+      p.x = fmaf(ac[0][k], ac[0][k], as[0][k] * as[0][k]);
+      p.y = fmaf(ac[1][k], ac[1][k], as[1][k] * as[1][k]);
+      p.z = fmaf(ac[2][k], ac[2][k], as[2][k] * as[2][k]);
+      p.w = fmaf(ac[3][k], ac[3][k], as[3][k] * as[3][k]);
+      *reinterpret_cast<float4*>(Pw + (bg * kBinsPerGroup + k) * kTileFrames + 4 * fg) = p;
+    }
+    __syncthreads();
+
+    // Sparse mel projection (<= 2 adjacent taps per filter), dB numerator, running max.
+    {
+      const int t = tid & (kTileFrames - 1);
+      const int f = f0 + t;
+      const int halves = kMelThreads / kTileFrames;
+      const int per = (a.n_mels + halves - 1) / halves;
+      const int m0 = (tid / kTileFrames) * per;
+      const int m1 = min(a.n_mels, m0 + per);
+      if (f < a.n_frames) {
+        for (int m = m0; m < m1; ++m) {
+          const int k0 = mk0[m];
+          const float v = fmaf(mw1[m], Pw[(k0 + 1) * kTileFrames + t], mw0[m] * Pw[k0 * kTileFrames + t]);
+          vmax = fmaxf(vmax, v);
+          if (f < a.n_time)
+            qbase[(long long)m * a.n_time + f] = 3.0102999566398120f * __log2f(fmaxf(a.amin, v));
+        }
+      }
+    }
+    __syncthreads();
+  }
+
+  // Frames beyond the kept width (frame 256 of 257) only contribute to the pair maximum.
+  const int n_extra = a.n_frames - n_tiles * kTileFrames;
+  if (n_extra > 0) {
+    float* Px = tile;  // [n_extra][kBinSlots]
+    for (int i = tid; i < n_extra * kBinSlots; i += kMelThreads) {
+      const int x = i / kBinSlots, ks = i % kBinSlots;
+      const int c = (n_tiles * kTileFrames + x) * a.hop;
+      const int g = ks / kBinsPerGroup, kk = ks % kBinsPerGroup;
+      float re = 0.f, im = 0.f;
+      for (int m = 0; m < kFold; ++m) {
+        const float yp = padded_sample(y, c + m, a.crop, a.pad_mode);
+        const float ym = m ? padded_sample(y, c - m, a.crop, a.pad_mode) : 0.f;
+        const float e = wh[m] * (yp + ym), o = m ? wh[m] * (yp - ym) : 0.f;
+        re = fmaf(e, cos_s[(m * kBinGroups + g) * kGroupPitch + kk], re);
+        im = fmaf(o, sin_s[(m * kBinGroups + g) * kGroupPitch + kk], im);
+      }
+      Px[i] = fmaf(re, re, im * im);
+    }
+    __syncthreads();
+    for (int i = tid; i < n_extra * a.n_mels; i += kMelThreads) {
+      const int x = i / a.n_mels, m = i % a.n_mels;
+      const int k0 = mk0[m];
+      vmax = fmaxf(vmax, fmaf(mw1[m], Px[x * kBinSlots + k0 + 1], mw0[m] * Px[x * kBinSlots + k0]));
+    }
+  }
+
+  vmax = warp_max_nan(vmax);
+  __syncthreads();
+  if (lane == 0) red_a[warp] = vmax;
+  __syncthreads();
+  if (tid == 0) {
+    float v = red_a[0];
+    for (int w = 1; w < kMelThreads / 32; ++w) v = max_nan(v, red_a[w]);
+    a.refdb[rec * a.n_pairs + pair] = 3.0102999566398120f * __log2f(fmaxf(a.amin, v));
+  }
+}
+
+// out[rec][mel][t][chain] = mean over the chain's pairs of (max(q - ref, -top_db) + off)/scale
+__global__ void __launch_bounds__(256) melspec_combine_kernel(const MelArgs a, long long n_pix) {
+  const long long pix = blockIdx.x * 256LL + threadIdx.x;  // (rec, mel, t)
+  if (pix >= n_pix) return;
+  const int per_rec = a.n_mels * a.n_time;
+  const long long rec = pix / per_rec;
+  const int mt = (int)(pix - rec * per_rec);
+  const float* q = a.q + rec * a.n_pairs * (long long)per_rec + mt;
+  const float* ref = a.refdb + rec * a.n_pairs;
+  float* o = a.out + pix * a.n_chains;
+  const float inv_ppc = 1.0f / (float)a.ppc;
+  for (int c = 0; c < a.n_chains; c += 4) {
+    float v[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+    for (int cc = 0; cc < 4; ++cc) {
+      if (c + cc < a.n_chains) {
+        float s = 0.f;
+        for (int p = 0; p < a.ppc; ++p) {
+          const int pr = (c + cc) * a.ppc + p;
+          const float db = fmaxf(__ldg(q + (long long)pr * per_rec) - ref[pr], -a.top_db);
+          s += (db + a.db_offset) * a.inv_db_scale;
+        }
+        v[cc] = s * inv_ppc;
+      }
+    }
+    if (a.n_chains - c >= 4 && (a.n_chains & 3) == 0) {
+      st_stream_f4(o + c, make_float4(v[0], v[1], v[2], v[3]));
+    } else {
+      for (int cc = 0; cc < 4 && c + cc < a.n_chains; ++cc) o[c + cc] = v[cc];
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------- host
+static double hz_to_mel(double f) {
+  const double f_sp = 200.0 / 3, min_log_hz = 1000.0, min_log_mel = min_log_hz / f_sp;
+  const double logstep = log(6.4) / 27.0;
+  return f >= min_log_hz ? min_log_mel + log(f / min_log_hz) / logstep : f / f_sp;
+}
+static double mel_to_hz(double m) {
+  const double f_sp = 200.0 / 3, min_log_hz = 1000.0, min_log_mel = min_log_hz / f_sp;
+  const double logstep = log(6.4) / 27.0;
+  return m >= min_log_mel ? min_log_hz * exp(logstep * (m - min_log_mel)) : f_sp * m;
+}
+
+// librosa.filters.mel(htk=False, norm='slaney', dtype=float32), row-major (n_mels, n_fft/2+1).
+static void slaney_filterbank(const eegspec_mel_params& p, std::vector<float>& w) {
+  const int nb = p.n_fft / 2 + 1, nm = p.n_mels;
+  std::vector<double> fftf(nb), melf(nm + 2);
+  const double val = 1.0 / (p.n_fft * (1.0 / p.sr));
+  for (int k = 0; k < nb; ++k) fftf[k] = k * val;
+  const double m_lo = hz_to_mel(p.fmin), m_hi = hz_to_mel(p.fmax);
+  const double step = (m_hi - m_lo) / (nm + 1);
+  for (int i = 0; i < nm + 2; ++i) melf[i] = mel_to_hz(i == nm + 1 ? m_hi : i * step + m_lo);
+  w.assign((size_t)nm * nb, 0.f);
+  for (int i = 0; i < nm; ++i) {
+    const double fd0 = melf[i + 1] - melf[i], fd1 = melf[i + 2] - melf[i + 1];
+    const double enorm = 2.0 / (melf[i + 2] - melf[i]);
+    for (int k = 0; k < nb; ++k) {
+      const double lower = -(melf[i] - fftf[k]) / fd0;
+      const double upper = (melf[i + 2] - fftf[k]) / fd1;
+      const float tri = (float)fmax(0.0, fmin(lower, upper));
+      w[(size_t)i * nb + k] = (float)((double)tri * enorm);
+    }
+  }
+}
+
+struct MelHostTables {
+  MelGeometry g;
+  std::vector<float> cos_t, sin_t, win_half, w0, w1;
+  std::vector<int> k0;
+};
+
+static int validate(const eegspec_mel_params* p) {
+  if (!p) return EEGSPEC_EINVAL;
+  if (p->sr <= 0 || p->n_fft <= 0 || p->n_mels <= 0 || p->crop <= 0 || p->n_time_div <= 0)
+    return EEGSPEC_EINVAL;
+  if (p->n_chains <= 0 || p->pairs_per_chain <= 0 ||
+      p->n_chains * p->pairs_per_chain > EEGSPEC_MAX_PAIRS)
+    return EEGSPEC_EINVAL;
+  if (!(p->fmax > p->fmin) || p->fmin < 0 || p->fmax > p->sr * 0.5f) return EEGSPEC_EINVAL;
+  if (!(p->db_scale != 0.f) || !(p->amin > 0.f)) return EEGSPEC_EINVAL;
+  if (p->win_length != 2 * kFold || p->n_fft < p->win_length) return EEGSPEC_EUNSUPPORTED;
+  if (p->n_mels > kMaxMels || p->crop > kMaxCrop || p->crop < p->win_length) return EEGSPEC_EUNSUPPORTED;
+  if (p->pad_mode != 0 && p->pad_mode != 1) return EEGSPEC_EUNSUPPORTED;
+  if (p->engine < 0 || p->engine > 1) return EEGSPEC_EUNSUPPORTED;
+  return EEGSPEC_OK;
+}
+
+static int build_host_tables(const eegspec_mel_params& p, MelHostTables& h) {
+  const int hop = p.hop > 0 ? p.hop : p.crop / p.n_time_div;
+  if (hop <= 0) return EEGSPEC_EINVAL;
+  h.g.hop = hop;
+  h.g.n_frames = 1 + p.crop / hop;  // centred: 1 + (crop + n_fft - n_fft)//hop
+  h.g.n_time = (h.g.n_frames / 32) * 32;
+  h.g.n_pairs = p.n_chains * p.pairs_per_chain;
+  if (h.g.n_time <= 0) return EEGSPEC_ESHORT;
+  if (h.g.n_frames - h.g.n_time > 2 * kFold * kTileFrames / kBinSlots) return EEGSPEC_EUNSUPPORTED;
+
+  std::vector<float> fb;
+  slaney_filterbank(p, fb);
+  const int nb = p.n_fft / 2 + 1;
+  int k_lo = nb, k_hi = -1;
+  for (int i = 0; i < p.n_mels; ++i)
+    for (int k = 0; k < nb; ++k)
+      if (fb[(size_t)i * nb + k] > 0.f) { k_lo = k < k_lo ? k : k_lo; k_hi = k > k_hi ? k : k_hi; }
+  if (k_hi < 0) { k_lo = 0; k_hi = 0; }
+  if (k_hi - k_lo + 1 > kBinSlots - 1) return EEGSPEC_EUNSUPPORTED;
+  h.g.k_lo = k_lo;
+  h.g.k_hi = k_hi;
+
+  h.k0.assign(p.n_mels, 0);
+  h.w0.assign(p.n_mels, 0.f);
+  h.w1.assign(p.n_mels, 0.f);
+  for (int i = 0; i < p.n_mels; ++i) {
+    int first = -1, last = -1;
+    for (int k = 0; k < nb; ++k)
+      if (fb[(size_t)i * nb + k] > 0.f) { if (first < 0) first = k; last = k; }
+    if (first < 0) continue;                       // empty filter: weight 0 on slot 0
+    if (last - first > 1) return EEGSPEC_EUNSUPPORTED;  // more than two taps per filter
+    h.k0[i] = first - k_lo;
+    h.w0[i] = fb[(size_t)i * nb + first];
+    h.w1[i] = last > first ? fb[(size_t)i * nb + last] : 0.f;
+  }
+
+  const size_t tsz = (size_t)kFold * kBinGroups * kGroupPitch;
+  h.cos_t.assign(tsz, 0.f);
+  h.sin_t.assign(tsz, 0.f);
+  const double theta = 2.0 * M_PI / p.n_fft;
+  for (int m = 0; m < kFold; ++m)
+    for (int ks = 0; ks <= k_hi - k_lo; ++ks) {
+      const int g = ks / kBinsPerGroup, kk = ks % kBinsPerGroup;
+      // reduce k*m modulo n_fft before the trig call: exact in integers
+      const long long km = ((long long)(k_lo + ks) * m) % p.n_fft;
+      h.cos_t[((size_t)m * kBinGroups + g) * kGroupPitch + kk] = (float)cos(theta * km);
+      h.sin_t[((size_t)m * kBinGroups + g) * kGroupPitch + kk] = (float)sin(theta * km);
+    }
+  h.win_half.assign(kFold, 0.f);
+  for (int m = 0; m < kFold; ++m)
+    h.win_half[m] = (float)(0.5 - 0.5 * cos(2.0 * M_PI * (kFold + m) / (2.0 * kFold)));
+  return EEGSPEC_OK;
+}
+
+int melspec_geometry(const eegspec_mel_params* p, MelGeometry* g) {
+  int rc = validate(p);
+  if (rc != EEGSPEC_OK) return rc;
+  MelHostTables h;
+  rc = build_host_tables(*p, h);
+  if (rc == EEGSPEC_OK && g) *g = h.g;
+  return rc;
+}
+
+struct TableKey {
+  int dev, sr, n_fft, win_length, n_mels;
+  float fmin, fmax;
+  bool operator==(const TableKey& o) const {
+    return dev == o.dev && sr == o.sr && n_fft == o.n_fft && win_length == o.win_length &&
+           n_mels == o.n_mels && fmin == o.fmin && fmax == o.fmax;
+  }
+};
+struct TableEntry { TableKey key; MelTables dev; MelGeometry g; };
+
+static std::mutex g_table_mu;
+static std::vector<TableEntry> g_tables;
+
+template <typename T>
+static cudaError_t upload(T** dst, const std::vector<T>& src) {
+  cudaError_t e = cudaMalloc(reinterpret_cast<void**>(dst), src.size() * sizeof(T));
+  if (e != cudaSuccess) return e;
+  return cudaMemcpy(*dst, src.data(), src.size() * sizeof(T), cudaMemcpyHostToDevice);
+}
+
+// Device tables for (device, filterbank parameters); built once, kept for the process lifetime.
+static int device_tables(const eegspec_mel_params& p, MelTables* out, MelGeometry* g) {
+  int dev = 0;
+  cudaError_t ce = cudaGetDevice(&dev);
+  if (ce != cudaSuccess) return (int)ce;
+  MelHostTables h;
+  int rc = build_host_tables(p, h);
+  if (rc != EEGSPEC_OK) return rc;
+  *g = h.g;
+  const TableKey key{dev, p.sr, p.n_fft, p.win_length, p.n_mels, p.fmin, p.fmax};
+  std::lock_guard<std::mutex> lock(g_table_mu);
+  for (const TableEntry& e : g_tables)
+    if (e.key == key) { *out = e.dev; return EEGSPEC_OK; }
+  TableEntry e;
+  e.key = key;
+  e.g = h.g;
+  if ((ce = upload(&e.dev.cos_t, h.cos_t)) != cudaSuccess) return (int)ce;
+  if ((ce = upload(&e.dev.sin_t, h.sin_t)) != cudaSuccess) return (int)ce;
+  if ((ce = upload(&e.dev.win_half, h.win_half)) != cudaSuccess) return (int)ce;
+  if ((ce = upload(&e.dev.mel_k0, h.k0)) != cudaSuccess) return (int)ce;
+  if ((ce = upload(&e.dev.mel_w0, h.w0)) != cudaSuccess) return (int)ce;
+  if ((ce = upload(&e.dev.mel_w1, h.w1)) != cudaSuccess) return (int)ce;
+  g_tables.push_back(e);
+  *out = e.dev;
+  return EEGSPEC_OK;
+}
+
+constexpr long long kMelChunk = 256;  // records per scratch pass
+
+static size_t per_record_scratch(const eegspec_mel_params& p, const MelGeometry& g) {
+  const size_t q = (size_t)g.n_pairs * p.n_mels * g.n_time * sizeof(float);
+  const size_t r = (size_t)g.n_pairs * sizeof(float);
+  return q + ((r + 15) & ~(size_t)15);
+}
+
+size_t melspec_workspace(long long batch, const eegspec_mel_params* p) {
+  MelGeometry g;
+  if (batch <= 0 || melspec_geometry(p, &g) != EEGSPEC_OK) return 0;
+  const long long chunk = batch < kMelChunk ? batch : kMelChunk;
+  return per_record_scratch(*p, g) * (size_t)chunk;
+}
+
+static size_t pair_kernel_smem(const eegspec_mel_params& p) {
+  size_t f = 0;
+  f += 2 * (size_t)kFold * kBinGroups * kGroupPitch;   // cos, sin
+  f += 2 * (size_t)kFold * kTileFrames;                // E | O
+  f += (size_t)((p.crop + 3) & ~3);                    // y
+  f += kFold + 2 * kMaxMels;                           // wh, mw0, mw1
+  return f * sizeof(float) + kMaxMels * sizeof(int);
+}
+
+int melspec_launch(const float* eeg, long long batch, int n_ch, long long length,
+                   long long rec_stride, const eegspec_mel_params* p, float* out, void* workspace,
+                   size_t workspace_bytes, cudaStream_t st) {
+  int rc = validate(p);
+  if (rc != EEGSPEC_OK) return rc;
+  if (!eeg || !out || batch <= 0 || n_ch <= 0) return EEGSPEC_EINVAL;
+  if (length < p->crop) return EEGSPEC_ESHORT;
+  if (rec_stride < (long long)n_ch * length) return EEGSPEC_EINVAL;
+  if (reinterpret_cast<uintptr_t>(out) & 15) return EEGSPEC_EALIGN;
+  const int n_pairs = p->n_chains * p->pairs_per_chain;
+  for (int i = 0; i < n_pairs; ++i)
+    if (p->pair_a[i] < 0 || p->pair_a[i] >= n_ch || p->pair_b[i] < 0 || p->pair_b[i] >= n_ch)
+      return EEGSPEC_EINVAL;
+
+  MelArgs a;
+  MelGeometry g;
+  if ((rc = device_tables(*p, &a.t, &g)) != EEGSPEC_OK) return rc;
+  const long long chunk = batch < kMelChunk ? batch : kMelChunk;
+  const size_t need = per_record_scratch(*p, g) * (size_t)chunk;
+  if (!workspace || workspace_bytes < need) return EEGSPEC_EWORKSPACE;
+  if (reinterpret_cast<uintptr_t>(workspace) & 15) return EEGSPEC_EALIGN;
+
+  a.rec_stride = rec_stride;
+  a.ch_stride = p->time_major ? 1 : length;
+  a.t_stride = p->time_major ? n_ch : 1;
+  a.length = length;
+  a.crop = p->crop;
+  a.crop_off = (int)((length - p->crop) / 2);   // cfg_utils.py:369-371
+  a.hop = g.hop;
+  a.n_frames = g.n_frames;
+  a.n_time = g.n_time;
+  a.n_mels = p->n_mels;
+  a.n_pairs = n_pairs;
+  a.n_chains = p->n_chains;
+  a.ppc = p->pairs_per_chain;
+  a.pad_mode = p->pad_mode;
+  a.amin = p->amin;
+  a.top_db = p->top_db;
+  a.db_offset = p->db_offset;
+  a.inv_db_scale = 1.0f / p->db_scale;
+  for (int i = 0; i < EEGSPEC_MAX_PAIRS; ++i) {
+    a.pair_a[i] = i < n_pairs ? p->pair_a[i] : 0;
+    a.pair_b[i] = i < n_pairs ? p->pair_b[i] : 0;
+  }
+
+  static bool configured[64] = {};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  const size_t smem = pair_kernel_smem(*p);
+  if (dev >= 0 && dev < 64 && !configured[dev]) {
+    cudaError_t e = cudaFuncSetAttribute(melspec_pair_kernel,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+    if (e != cudaSuccess) return (int)e;
+    configured[dev] = true;
+  }
+  if (smem > 220 * 1024) return EEGSPEC_EUNSUPPORTED;
+
+  const size_t q_bytes = (size_t)chunk * n_pairs * p->n_mels * g.n_time * sizeof(float);
+  for (long long r0 = 0; r0 < batch; r0 += chunk) {
+    const long long nb = batch - r0 < chunk ? batch - r0 : chunk;
+    a.eeg = eeg + r0 * rec_stride;
+    a.q = static_cast<float*>(workspace);
+    a.refdb = reinterpret_cast<float*>(static_cast<char*>(workspace) + q_bytes);
+    a.out = out + r0 * (long long)p->n_mels * g.n_time * p->n_chains;
+    melspec_pair_kernel<<<dim3(n_pairs, (unsigned)nb), kMelThreads, smem, st>>>(a);
+    count_launch();
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return (int)e;
+    const long long n_pix = nb * p->n_mels * g.n_time;
+    melspec_combine_kernel<<<(unsigned)((n_pix + 255) / 256), 256, 0, st>>>(a, n_pix);
+    count_launch();
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return (int)e;
+  }
+  return EEGSPEC_OK;
+}
+
+}  // namespace eegspec

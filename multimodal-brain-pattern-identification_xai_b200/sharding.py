@@ -1,0 +1,46 @@
+"""Record sharding across GPUs: one process per GPU, contiguous slices, no collective.
+
+Every (record, channel) row of mode R and every record of mode N is independent (the
+normalisation of /root/reference/root/src/utils/DiffEEG_utils.py:72-74 is per row), so rank r
+of G simply takes records ``[bounds(r), bounds(r+1))``.  The only optional exchange is a final
+all-gather of the outputs for a consumer that wants them replicated.
+"""
+from __future__ import annotations
+
+import torch
+
+
+def shard_bounds(n_records: int, world_size: int, rank: int) -> tuple[int, int]:
+    """Contiguous slice of rank ``rank``; the remainder goes to the low ranks."""
+    if world_size <= 0 or not 0 <= rank < world_size or n_records < 0:
+        raise ValueError("bad shard request")
+    base, rem = divmod(n_records, world_size)
+    lo = rank * base + min(rank, rem)
+    return lo, lo + base + (1 if rank < rem else 0)
+
+
+def shard_slice(records, world_size: int, rank: int):
+    lo, hi = shard_bounds(len(records), world_size, rank)
+    return records[lo:hi]
+
+
+def gather_spectrograms(local: torch.Tensor, n_records: int, group=None) -> torch.Tensor:
+    """All-gather per-rank outputs back into record order (NCCL on GPUs, gloo on CPU).
+
+    Shards may differ by one record, so every rank pads to the largest shard, one
+    ``all_gather_into_tensor`` moves the data, and the padding is dropped."""
+    import torch.distributed as dist
+
+    world = dist.get_world_size(group)
+    sizes = [shard_bounds(n_records, world, r) for r in range(world)]
+    biggest = max(hi - lo for lo, hi in sizes)
+    padded = local
+    if local.shape[0] < biggest:
+        pad = torch.zeros((biggest - local.shape[0],) + tuple(local.shape[1:]),
+                          dtype=local.dtype, device=local.device)
+        padded = torch.cat([local, pad], dim=0)
+    out = torch.empty((world * biggest,) + tuple(local.shape[1:]), dtype=local.dtype,
+                      device=local.device)
+    dist.all_gather_into_tensor(out, padded.contiguous(), group=group)
+    parts = [out[r * biggest: r * biggest + (hi - lo)] for r, (lo, hi) in enumerate(sizes)]
+    return torch.cat(parts, dim=0)

@@ -1,0 +1,125 @@
+"""Generate the golden vectors under tests/golden/ (run in the BUILD container only).
+
+    python tests/golden/make_golden.py
+
+* ``stft_golden.npz``   -- inputs and outputs of the REFERENCE's own ``compute_stft`` /
+  ``compute_stft_single`` (``/root/reference/root/src/utils/DiffEEG_utils.py:27-76, 504-509``),
+  executed here through ``oracle/ref_extract.py`` (AST lift, nothing copied).  These pin the
+  mode-R oracle and the CUDA path.
+* ``melspec_golden.npz`` -- mode N has no reference implementation (parity UNPINNED, see
+  ``oracle/melspec_oracle.py``); the vectors come from the oracle restatement and guard the
+  CUDA path and the oracle itself against regressions.  The montage facts inside are read
+  from the reference's ``config.yml``.
+
+Versions used to generate the committed files are stored inside them.
+"""
+from __future__ import annotations
+
+import os
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
+
+from oracle import melspec_oracle as mo  # noqa: E402
+from oracle import ref_extract as rx  # noqa: E402
+
+
+def eeg_like(rng, shape, walk=0.3, noise=1.0):
+    x = np.cumsum(rng.standard_normal(shape), axis=-1) * walk
+    t = np.arange(shape[-1]) / 200.0
+    x = x + 10.0 * np.sin(2 * np.pi * 10.0 * t) + noise * rng.standard_normal(shape)
+    return np.clip(x, -1024, 1024).astype(np.float32)
+
+
+STFT_CASES = {
+    # name: (B, C, L, nperseg, noverlap, kind)
+    "diffeeg_64_32": (2, 2, 2000, 64, 32, "eeg"),
+    "hms50s_64_32": (1, 2, 10000, 64, 32, "eeg"),
+    "nfft128": (1, 1, 2000, 128, 64, "eeg"),
+    "hop16": (1, 1, 2000, 64, 48, "randn"),
+    "one_window": (1, 1, 64, 64, 32, "randn"),
+    "nfft16": (1, 2, 2000, 16, 8, "randn"),
+    "nfft256_odd_len": (1, 1, 2001, 256, 100, "eeg"),
+    "flat_rows": (1, 3, 2000, 64, 32, "flat"),
+    "nan_sample": (1, 2, 2000, 64, 32, "nan"),
+    "decimating": (1, 1, 70000, 64, 32, "eeg"),
+    "gather": (1, 1, 200000, 64, 32, "eeg"),
+}
+
+
+def make_stft():
+    import scipy
+    import torch
+
+    ref = rx.load_reference_compute_stft()
+    ref_single = rx.load_reference_compute_stft_single()
+    rng = np.random.default_rng(20261104)
+    out = {}
+    for name, (b, c, length, nperseg, noverlap, kind) in STFT_CASES.items():
+        if kind == "randn":
+            x = rng.standard_normal((b, c, length)).astype(np.float32)
+        else:
+            x = eeg_like(rng, (b, c, length))
+        if kind == "flat":
+            x[0, 0] = 0.0            # all-zero channel
+            x[0, 1] = 37.5           # constant channel
+        if kind == "nan":
+            x[0, 0, 777] = np.nan    # poisons every row of channel 0, leaves channel 1 alone
+        cfg = rx.make_config(nperseg, noverlap)
+        y = ref(torch.from_numpy(x), cfg).numpy()
+        assert y.dtype == np.float32
+        out[f"{name}/x"] = x
+        out[f"{name}/y"] = y
+        out[f"{name}/cfg"] = np.array([nperseg, noverlap], dtype=np.int64)
+    x = eeg_like(rng, (2000,))
+    out["single/x"] = x
+    out["single/y"] = ref_single(torch.from_numpy(x), rx.make_config(64, 32)).astype(np.float32)
+    out["versions"] = np.array([f"scipy {scipy.__version__}", f"numpy {np.__version__}",
+                                f"torch {torch.__version__}"])
+    np.savez_compressed(os.path.join(HERE, "stft_golden.npz"), **out)
+    print("stft_golden.npz:", {k: v.shape for k, v in out.items() if k.endswith("/y")})
+
+
+def make_melspec():
+    import yaml
+
+    rng = np.random.default_rng(20261105)
+    out = {}
+    x = eeg_like(rng, (1, 20, 10000))
+    x[:, 19] = (np.arange(10000) % 200 < 3) * 500.0            # EKG-like spike train
+    out["clean/x"] = x
+    out["clean/y"] = mo.eeg_to_spectrogram_batch_oracle(x)
+    out["clean/y_reflect"] = mo.eeg_to_spectrogram_batch_oracle(x, pad_mode="reflect")
+
+    xn = eeg_like(rng, (1, 20, 10400))                           # longer than the crop window
+    holes = rng.random((10400,)) < 0.005
+    xn[0, 4, holes] = np.nan                                     # F7: touches LL pairs 0 and 1
+    xn[0, 13, 100:900] = np.nan                                  # C4: a run of NaNs
+    xn[0, 17] = np.nan                                           # T6 entirely missing
+    out["nan/x"] = xn
+    out["nan/y"] = mo.eeg_to_spectrogram_batch_oracle(xn)
+
+    xq = eeg_like(rng, (1, 20, 10000)) * np.float32(1e-3)
+    xq[0, 0, 5000:5040] += 900.0                                 # electrode pop: > 80 dB range
+    xq[0, 11] = 0.0
+    xq[0, 12] = 0.0                                              # Fp2-F4 identically zero
+    out["range/x"] = xq
+    out["range/y"] = mo.eeg_to_spectrogram_batch_oracle(xq)
+
+    with open(os.path.join(rx.REFERENCE_ROOT, "root", "config", "config.yml")) as fh:
+        cfg = yaml.safe_load(fh)
+    out["ref_eeg_columns"] = np.array(cfg["EEG_COLUMNS"])
+    out["ref_map_features"] = np.array(cfg["map_features"])
+    out["versions"] = np.array([f"numpy {np.__version__}"])
+    np.savez_compressed(os.path.join(HERE, "melspec_golden.npz"), **out)
+    print("melspec_golden.npz:", {k: v.shape for k, v in out.items() if "/y" in k})
+
+
+if __name__ == "__main__":
+    if not rx.reference_available():
+        raise SystemExit("/root/reference is not mounted: golden vectors can only be made in the build container")
+    make_stft()
+    make_melspec()

@@ -1,0 +1,73 @@
+"""CPU: the mode-N oracle -- front half pinned to the reference, back half cross-checked."""
+import os
+
+import numpy as np
+import pytest
+
+from conftest import eeg_like
+from oracle import melspec_oracle as mo
+from oracle import ref_extract as rx
+
+
+def test_montage_matches_reference_config(melspec_golden):
+    assert list(melspec_golden["ref_eeg_columns"]) == mo.EEG_COLUMNS
+    assert [tuple(p) for p in melspec_golden["ref_map_features"]] == mo.MAP_FEATURES
+
+
+@pytest.mark.skipif(not rx.reference_available(), reason="/root/reference not mounted")
+def test_montage_matches_live_reference_yaml():
+    import yaml
+
+    with open(os.path.join(rx.REFERENCE_ROOT, "root", "config", "config.yml")) as fh:
+        cfg = yaml.safe_load(fh)
+    assert cfg["EEG_COLUMNS"] == mo.EEG_COLUMNS
+    assert [tuple(p) for p in cfg["map_features"]] == mo.MAP_FEATURES
+
+
+def test_crop_and_nan_fill_follow_reference_idiom():
+    assert mo.crop_offset(10000) == 0 and mo.crop_offset(18000) == 4000 and mo.crop_offset(10001) == 0
+    x = np.array([1.0, np.nan, 3.0, np.nan], np.float32)
+    np.testing.assert_array_equal(mo.fill_missing(x), np.array([1, 2, 3, 2], np.float32))
+    np.testing.assert_array_equal(mo.fill_missing(np.full(5, np.nan, np.float32)), np.zeros(5, np.float32))
+
+
+def test_filterbank_structure_and_torchaudio():
+    fb = mo.mel_filterbank()
+    nz = np.argwhere(fb > 0)
+    assert fb.shape == (128, 513) and nz[:, 1].min() == 1 and nz[:, 1].max() == 102
+    assert (fb > 0).sum(axis=1).max() <= 2
+    ta = pytest.importorskip("torchaudio")
+    ref = ta.functional.melscale_fbanks(513, 0.0, 20.0, 128, 200, norm="slaney", mel_scale="slaney").T.numpy()
+    assert np.abs(ref - fb).max() <= 1e-4 * fb.max()
+
+
+def test_stft_power_against_torch_stft():
+    import torch
+
+    rng = np.random.default_rng(3)
+    y = eeg_like(rng, (10000,))
+    win = torch.zeros(1024, dtype=torch.float64)
+    win[448:576] = torch.hann_window(128, periodic=True, dtype=torch.float64)
+    for mode in ("constant", "reflect"):
+        s = torch.stft(torch.from_numpy(y).double(), 1024, 39, 1024, window=win, center=True,
+                       pad_mode=mode, return_complex=True).abs() ** 2
+        p = mo.stft_power(y, pad_mode=mode)
+        assert p.shape == (513, 257)
+        assert np.abs(s.numpy() - p).max() <= 1e-6 * p.max()
+
+
+def test_oracle_reproduces_golden(melspec_golden):
+    for case, key, mode in [("clean", "y", "constant"), ("clean", "y_reflect", "reflect"),
+                            ("nan", "y", "constant"), ("range", "y", "constant")]:
+        got = mo.eeg_to_spectrogram_batch_oracle(melspec_golden[f"{case}/x"], pad_mode=mode)
+        np.testing.assert_allclose(got, melspec_golden[f"{case}/{key}"], rtol=0, atol=1e-6)
+
+
+def test_image_properties(melspec_golden):
+    y = melspec_golden["range/y"]
+    assert y.shape == (1, 128, 256, 4) and y.dtype == np.float32
+    assert y.max() <= 1.0 + 1e-6 and y.min() >= -1.0 - 1e-6   # dB in [-80, 0] -> [-1, 1]
+    # the electrode pop on Fp1 drives quiet pixels of pair Fp1-F7 onto the top_db floor
+    x = melspec_golden["range/x"][0]
+    db = mo.pair_melspec_db(mo.fill_missing(x[0] - x[4]))
+    assert (db == -80.0).mean() > 0.05 and db.max() == 0.0
