@@ -1,0 +1,30 @@
+#!/usr/bin/env bash
+# Profiling recipe of this repo (run on the B200 box through gpurun; see B200_PROFILING.md):
+#   gpurun --timeout 1500 -- 'bash profiles/capture.sh r1'
+# 1. the plain bench (its JSON line is the only number that counts),
+# 2. the ncu launch list of the same transform legs (cold-cache, serialised: compare shares),
+# 3. one `ncu --set full` capture per hot kernel.
+set -u
+TAG=${1:-r1}
+OUT=gpurun_out
+mkdir -p $OUT
+CMD="python bench.py --steps 2 --warmup 3 --legs n,r"
+
+python bench.py --steps 10 --warmup 3 > $OUT/bench_$TAG.json 2> $OUT/bench_$TAG.err
+echo "bench rc=$?"; tail -c 600 $OUT/bench_$TAG.err
+
+$CMD > $OUT/plain_$TAG.log 2>&1 &&
+ncu --metrics gpu__time_duration.sum --clock-control none -c 800 --csv \
+    --log-file $OUT/launches_$TAG.csv $CMD > $OUT/ncu_launches_$TAG.log 2>&1
+echo "launch list rc=$?"
+
+cap() {  # name regex skip
+  ncu --set full --clock-control none --import-source on -k regex:$2 -s $3 -c 1 \
+      -f -o $OUT/prof_${TAG}_$1 $CMD > $OUT/ncu_$1_$TAG.log 2>&1
+  echo "capture $1 rc=$?"
+}
+cap melspec_pair melspec_pair_kernel 14
+cap melspec_combine melspec_combine_kernel 14
+cap stft_hms50s stft_image_kernel 3
+cap stft_diffeeg stft_image_kernel 8
+ls -la $OUT
