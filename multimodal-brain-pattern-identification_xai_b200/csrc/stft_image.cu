@@ -26,9 +26,9 @@ struct StftArgs {
   const float* x;
   float* out;
   float* ws;
-  long long rows, L, row_stride, n_frames, ws_stride, q_step;
+  long long rows, L, row_stride, n_frames, ws_stride, q_step, q32_step;
   int hop, half, n_slots, n_pad, gather, split, logmag_only, use_ws;
-  int out_cols, D, r_step, small_index;
+  int out_cols, D, r_step, r32_step, small_index, ends_only, n_items;
   float inv_d, eps;
 };
 
@@ -50,17 +50,14 @@ __device__ __forceinline__ void bracket_of(const StftArgs& a, long long j, long 
   }
 }
 
-// Interpolated (un-normalised) value of column j on knot row Sf.
-__device__ __forceinline__ float column_value(const StftArgs& a, const float* Sf, long long j) {
-  long long i;
-  int rem;
-  bracket_of(a, j, i, rem);
-  const long long lo = a.gather ? 2 * j : i;
-  const float s0 = Sf[lo], s1 = Sf[lo + 1];
-  return fmaf(s1 - s0, (float)rem * a.inv_d, s0);
+// ceil(a / b) for the first / last column of a linear segment
+__device__ __forceinline__ long long ceil_div(const StftArgs& a, long long num, long long den) {
+  if (a.small_index) return ((unsigned)num + (unsigned)den - 1u) / (unsigned)den;
+  return (num + den - 1) / den;
 }
 
-template <int LOG2N>
+// STRIDE = floats between consecutive knots of one frequency row (2: {value, delta} pairs).
+template <int LOG2N, int STRIDE>
 __device__ __forceinline__ void fft_phase(const StftArgs& a, const float* __restrict__ xrow,
                                           float* S, const float* win, const float2* tw,
                                           const float2* utw, float2* zs_all) {
@@ -68,7 +65,7 @@ __device__ __forceinline__ void fft_phase(const StftArgs& a, const float* __rest
   constexpr int LPF = P < 32 ? P : 32;       // lanes per frame
   constexpr int NPL = P < 32 ? 1 : P / 32;   // complex points per lane
   constexpr int FPW = 32 / LPF;              // frames per warp pass
-  constexpr int NSH = LOG2P - (NPL > 1 ? (LOG2P - 5) : 0);  // shuffle stages
+  constexpr int NSH = NPL > 1 ? 5 : LOG2P;   // shuffle stages
   constexpr bool HOIST = (NPL == 1);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
   const int le = lane % LPF, grp = lane / LPF;
@@ -87,27 +84,67 @@ __device__ __forceinline__ void fft_phase(const StftArgs& a, const float* __rest
     }
   }
 
-  for (int base = warp * FPW; base < a.n_slots; base += nwarps * FPW) {
+  // Per-lane output rows (k = le + LPF*r) are loop invariant: hoist their base pointers.
+  float* Sk[NPL];
+#pragma unroll
+  for (int r = 0; r < NPL; ++r) Sk[r] = S + (long long)(le + LPF * r) * a.n_pad * STRIDE;
+  float* Snyq = S + (long long)P * a.n_pad * STRIDE;
+  const bool small = a.L < (1LL << 30) && !a.gather;   // 32-bit sample indices
+
+  // Sample fetch for one slot: two values per complex point, zero outside [0, L).
+  auto fetch = [&](int slot, float (&v0)[NPL], float (&v1)[NPL]) {
+    const bool live = slot < a.n_slots;
+    if (small) {
+      const int s0 = slot * a.hop - a.half;
+      const int len = (int)a.L;
+      if (live && s0 >= 0 && s0 + N <= len) {
+#pragma unroll
+        for (int r = 0; r < NPL; ++r) {
+          const int i0 = s0 + 2 * (le * NPL + r);
+          v0[r] = __ldg(xrow + i0);
+          v1[r] = __ldg(xrow + i0 + 1);
+        }
+      } else {
+#pragma unroll
+        for (int r = 0; r < NPL; ++r) {
+          const int i0 = s0 + 2 * (le * NPL + r), i1 = i0 + 1;
+          v0[r] = (live && i0 >= 0 && i0 < len) ? __ldg(xrow + i0) : 0.f;
+          v1[r] = (live && i1 >= 0 && i1 < len) ? __ldg(xrow + i1) : 0.f;
+        }
+      }
+    } else {
+      long long frame = slot;
+      if (a.gather) {
+        int rem;
+        bracket_of(a, slot >> 1, frame, rem);
+        frame += (slot & 1);
+      }
+      const long long s0 = frame * a.hop - a.half;
+#pragma unroll
+      for (int r = 0; r < NPL; ++r) {
+        const long long i0 = s0 + 2 * (le * NPL + r), i1 = i0 + 1;
+        v0[r] = (live && i0 >= 0 && i0 < a.L) ? __ldg(xrow + i0) : 0.f;
+        v1[r] = (live && i1 >= 0 && i1 < a.L) ? __ldg(xrow + i1) : 0.f;
+      }
+    }
+  };
+
+  const int stride_slots = nwarps * FPW;
+  float nv0[NPL], nv1[NPL];
+  fetch(warp * FPW + grp, nv0, nv1);
+  for (int base = warp * FPW; base < a.n_slots; base += stride_slots) {
     const int slot = base + grp;
     const bool live = slot < a.n_slots;
-    long long frame = slot;
-    if (a.gather) {
-      int rem;
-      bracket_of(a, slot >> 1, frame, rem);
-      frame += (slot & 1);
-    }
-    const long long s0 = frame * a.hop - a.half;
 
     float2 z[NPL];
 #pragma unroll
     for (int r = 0; r < NPL; ++r) {
       const int e = le * NPL + r;
-      const long long i0 = s0 + 2 * e, i1 = i0 + 1;
-      const float v0 = (live && i0 >= 0 && i0 < a.L) ? __ldg(xrow + i0) : 0.f;
-      const float v1 = (live && i1 >= 0 && i1 < a.L) ? __ldg(xrow + i1) : 0.f;
       const float2 w = HOIST ? h_win : make_float2(win[2 * e], win[2 * e + 1]);
-      z[r] = make_float2(v0 * w.x, v1 * w.y);
+      z[r] = make_float2(nv0[r] * w.x, nv1[r] * w.y);
     }
+    // Software pipeline: the next frame's samples are in flight while this one is transformed.
+    if (base + stride_slots < a.n_slots) fetch(slot + stride_slots, nv0, nv1);
 
     // Decimation-in-frequency radix-2; element e ends up holding Z[bitrev(e)].
 #pragma unroll
@@ -116,22 +153,26 @@ __device__ __forceinline__ void fft_phase(const StftArgs& a, const float* __rest
       if (h >= NPL) {
         const int lm = h / NPL;
         const bool lower = (le & lm) != 0;
+        const float sgn = lower ? -1.f : 1.f;
 #pragma unroll
         for (int r = 0; r < NPL; ++r) {
           float2 o;
           o.x = __shfl_xor_sync(0xffffffffu, z[r].x, lm);
           o.y = __shfl_xor_sync(0xffffffffu, z[r].y, lm);
-          float2 t;
-          t.x = lower ? o.x - z[r].x : z[r].x + o.x;
-          t.y = lower ? o.y - z[r].y : z[r].y + o.y;
-          float2 w;
-          if constexpr (HOIST) {
-            w = h_tw[st];
+          // upper lane: own + partner; lower lane: partner - own
+          const float2 t = make_float2(fmaf(z[r].x, sgn, o.x), fmaf(z[r].y, sgn, o.y));
+          if (h == 1 && NPL == 1) {   // last stage of the 1-point path: twiddle is 1
+            z[r] = t;
           } else {
-            const int m = (le * NPL + r) % h;
-            w = lower ? tw[m * (P / (2 * h))] : make_float2(1.f, 0.f);
+            float2 w;
+            if constexpr (HOIST) {
+              w = h_tw[st];
+            } else {
+              const int m = (le * NPL + r) % h;
+              w = lower ? tw[m * (P / (2 * h))] : make_float2(1.f, 0.f);
+            }
+            z[r] = cmul(t, w);
           }
-          z[r] = cmul(t, w);
         }
       } else {
 #pragma unroll
@@ -140,7 +181,7 @@ __device__ __forceinline__ void fft_phase(const StftArgs& a, const float* __rest
             const float2 p = z[r], q = z[r + h];
             z[r] = make_float2(p.x + q.x, p.y + q.y);
             const float2 d = make_float2(p.x - q.x, p.y - q.y);
-            z[r + h] = cmul(d, tw[(r % h) * (P / (2 * h))]);
+            z[r + h] = (r % h == 0) ? d : cmul(d, tw[(r % h) * (P / (2 * h))]);
           }
         }
       }
@@ -163,38 +204,41 @@ __device__ __forceinline__ void fft_phase(const StftArgs& a, const float* __rest
       const float br = zk.x - zp.x, bi = zk.y + zp.y;
       const float ur = fmaf(w.x, br, w.y * bi), ui = fmaf(w.x, bi, -w.y * br);
       const float xr = 0.5f * (ar + ui), xi = 0.5f * (ai - ur);
-      const float mag = sqrtf(fmaf(xr, xr, xi * xi));
+      const float mag = sqrt_pos(fmaf(xr, xr, xi * xi));
       if (live) {
-        S[(long long)k * a.n_pad + slot] = log1pf(mag);
+        Sk[r][slot * STRIDE] = log1p_pos(mag);
         // Nyquist bin X[P] = Re Z[0] - Im Z[0]; log1p is applied in a separate pass.
-        if (k == 0) S[(long long)P * a.n_pad + slot] = fabsf(zk.x - zk.y);
+        if (k == 0) Snyq[slot * STRIDE] = fabsf(zk.x - zk.y);
       }
     }
     __syncwarp();
   }
 }
 
-constexpr int kStftThreads = 256;
+constexpr int kStftMaxThreads = 512;
 
 // MODE 0: knots in shared memory (the normal case); 1: knots in a global workspace slice
 // (very long rows); 2: log-magnitude only, knots written straight to the output.
 template <int LOG2N, int MODE>
-__global__ void __launch_bounds__(kStftThreads)
+__global__ void __launch_bounds__(kStftMaxThreads, (LOG2N <= 7 ? 2 : 1))
 stft_image_kernel(const StftArgs a) {
   constexpr int N = 1 << LOG2N, P = N / 2, F = P + 1;
   constexpr int LPF = P < 32 ? P : 32;
   constexpr int FPW = 32 / LPF;
+  constexpr int STRIDE = MODE == 2 ? 1 : 2;
   extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int nthreads = blockDim.x, nwarps = nthreads >> 5;
   float2* tw = reinterpret_cast<float2*>(smem_raw);                 // P/2 (>=1)
   float2* utw = tw + (P / 2 > 0 ? P / 2 : 1);                       // P
   float2* zs = utw + P;                                             // warps * FPW * P
-  float2* mm = zs + (kStftThreads / 32) * FPW * P;                  // F  (min, 1/(max-min+eps))
-  float* win = reinterpret_cast<float*>(mm + F);                    // N
-  float* S_sm = win + N;                                            // F * n_pad (when on chip)
+  float2* ends = zs + nwarps * FPW * P;                             // n_items when ends_only
+  float* win = reinterpret_cast<float*>(ends + (a.ends_only ? a.n_items : 0));  // N
+  int* rowflag = reinterpret_cast<int*>(win + N);                   // F + 1 (NaN rows, any)
+  float* S_sm = reinterpret_cast<float*>(rowflag + F + 1 + ((F + 1) & 1));      // F*n_pad*STRIDE
 
   const long long row = blockIdx.x / a.split;
   const int part = blockIdx.x % a.split;
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = kStftThreads / 32;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const float* __restrict__ xrow = a.x + row * a.row_stride;
 
   float* S;
@@ -203,56 +247,103 @@ stft_image_kernel(const StftArgs a) {
   else S = S_sm;
 
   // Tables.  Periodic Hann scaled by 1/sum(w) = 2/N (scipy scaling='spectrum', mode 'stft').
-  for (int j = tid; j < N; j += kStftThreads)
+  for (int j = tid; j < N; j += nthreads)
     win[j] = (0.5f - 0.5f * cospif(2.0f * j / N)) * (2.0f / N);
-  for (int k = tid; k < P / 2; k += kStftThreads)
+  for (int k = tid; k < P / 2; k += nthreads)
     tw[k] = make_float2(cospif(2.0f * k / P), -sinpif(2.0f * k / P));
-  for (int k = tid; k < P; k += kStftThreads)
+  for (int k = tid; k < P; k += nthreads)
     utw[k] = make_float2(cospif(2.0f * k / N), sinpif(2.0f * k / N));
+  if constexpr (MODE != 2) {
+    for (int f = tid; f <= F; f += nthreads) rowflag[f] = 0;
+    // First and last output column of every linear segment, as (knot slot, fraction): the
+    // extrema of a piecewise-linear row over the sampled columns can only sit there.
+    if (a.ends_only) {
+      // ends_only implies n_frames - 1 < out_cols / 2, so everything fits 32-bit integers.
+      // Segment seg covers columns [ceil(seg*D/nm1), ceil((seg+1)*D/nm1) - 1]; each thread walks a
+      // contiguous run of segments, carrying (seg*D) div/mod nm1 forward without dividing again.
+      const int nm1 = (int)a.n_frames - 1, D = a.D;
+      const int per = (nm1 + nthreads - 1) / nthreads;
+      const int seg0 = tid * per, seg1 = min(nm1, seg0 + per);
+      if (seg0 < seg1) {
+        const int dq = D / nm1, dr = D % nm1;
+        int q = (int)(((long long)seg0 * D) / nm1), r = (int)(((long long)seg0 * D) % nm1);
+        int jf = q + (r ? 1 : 0);                       // first column of seg0
+        for (int seg = seg0; seg < seg1; ++seg) {
+          q += dq; r += dr;
+          if (r >= nm1) { r -= nm1; ++q; }
+          const int jn = q + (r ? 1 : 0);               // first column of seg + 1
+          const int jl = (seg == nm1 - 1) ? D : jn - 1; // last column of seg
+          // column j sits at fraction (j*nm1 - seg*D)/D inside segment seg
+          ends[2 * seg] = make_float2(__int_as_float(seg * STRIDE), (float)(jf * nm1 - seg * D) * a.inv_d);
+          ends[2 * seg + 1] = make_float2(__int_as_float(seg * STRIDE), (float)(jl * nm1 - seg * D) * a.inv_d);
+          jf = jn;
+        }
+      }
+    }
+  }
   __syncthreads();
 
-  fft_phase<LOG2N>(a, xrow, S, win, tw, utw, zs);
+  fft_phase<LOG2N, STRIDE>(a, xrow, S, win, tw, utw, zs);
   __syncthreads();
 
-  for (int s = tid; s < a.n_slots; s += kStftThreads) {
-    float* p = S + (long long)P * a.n_pad + s;
-    *p = log1pf(*p);
+  for (int s = tid; s < a.n_slots; s += nthreads) {
+    float* p = S + ((long long)P * a.n_pad + s) * STRIDE;
+    *p = log1p_pos(*p);
   }
   if constexpr (MODE == 2) return;
   __syncthreads();
 
-  // Phase 2: per-frequency min/max of the interpolated row, then normalise the knots.
-  const bool ends_only = !a.gather && 2 * (a.n_frames - 1) < a.out_cols;
-  const long long n_items = ends_only ? 2 * (a.n_frames - 1) : a.out_cols;
+  // Phase 2: per-frequency min/max of the interpolated row; then every knot becomes the pair
+  // {normalised value, normalised delta to the next knot} so that phase 3 is one FFMA per pixel.
   const long long nm1 = a.n_frames - 1;
   for (int f = warp; f < F; f += nwarps) {
-    float* Sf = S + (long long)f * a.n_pad;
+    float* Sf = S + (long long)f * a.n_pad * STRIDE;
     float lo = __int_as_float(0x7f800000), hi = __int_as_float(0xff800000);
-    for (long long t = lane; t < n_items; t += 32) {
-      long long j = t;
-      if (ends_only) {
-        const long long seg = t >> 1;
-        if ((t & 1) == 0) j = (seg * a.D + nm1 - 1) / nm1;
-        else j = (seg == nm1 - 1) ? a.D : ((seg + 1) * a.D + nm1 - 1) / nm1 - 1;
+    if (a.ends_only) {
+      for (int t = lane; t < a.n_items; t += 32) {
+        const float2 e = ends[t];
+        const int o = __float_as_int(e.x);
+        const float s0 = Sf[o], s1 = Sf[o + STRIDE];
+        const float v = fmaf(s1 - s0, e.y, s0);
+        lo = min_nan(lo, v);
+        hi = max_nan(hi, v);
       }
-      const float v = column_value(a, Sf, j);
-      lo = min_nan(lo, v);
-      hi = max_nan(hi, v);
+    } else {
+      long long i;
+      int rem;
+      bracket_of(a, lane, i, rem);
+      for (int j = lane; j < a.out_cols; j += 32) {
+        const long long o = (a.gather ? 2LL * j : i) * STRIDE;
+        const float s0 = Sf[o], s1 = Sf[o + STRIDE];
+        const float v = fmaf(s1 - s0, (float)rem * a.inv_d, s0);
+        lo = min_nan(lo, v);
+        hi = max_nan(hi, v);
+        i += a.q32_step;
+        rem += a.r32_step;
+        if (rem >= a.D) { rem -= a.D; ++i; }
+        if (i >= nm1) { i = nm1 - 1; rem = a.D; }
+      }
     }
     lo = warp_min_nan(lo);
     hi = warp_max_nan(hi);
     const float inv = 1.0f / (hi - lo + a.eps);
+    if (lane == 0 && !(inv == inv)) { rowflag[f] = 1; rowflag[F] = 1; }
+    // deltas first (they read only the values), then the values in place
+    for (int s = lane; s < a.n_slots - 1; s += 32)
+      Sf[s * STRIDE + 1] = (Sf[(s + 1) * STRIDE] - Sf[s * STRIDE]) * inv;
+    if (lane == 0) Sf[(a.n_slots - 1) * STRIDE + 1] = 0.f;
     __syncwarp();
-    for (int s = lane; s < a.n_slots; s += 32) Sf[s] = (Sf[s] - lo) * inv;
+    for (int s = lane; s < a.n_slots; s += 32) Sf[s * STRIDE] = (Sf[s * STRIDE] - lo) * inv;
   }
   __syncthreads();
 
   // Phase 3: image write.  A thread keeps the four brackets of its column quad in registers
   // and walks the frequency rows; a warp emits one contiguous 512 B line per row.
   const int Q = a.out_cols >> 2;
-  const int q0 = (int)((long long)part * Q / a.split), q1 = (int)((long long)(part + 1) * Q / a.split);
+  const int q0 = (int)((unsigned)part * (unsigned)Q / (unsigned)a.split);
+  const int q1 = (int)((unsigned)(part + 1) * (unsigned)Q / (unsigned)a.split);
   float* __restrict__ orow = a.out + row * (long long)F * a.out_cols;
-  for (int q = q0 + tid; q < q1; q += kStftThreads) {
+  for (int q = q0 + tid; q < q1; q += nthreads) {
     int lo_i[4];
     float fr[4];
     {
@@ -270,30 +361,41 @@ stft_image_kernel(const StftArgs a) {
       }
     }
     float* o = orow + 4LL * q;
-    const float* Sf = S;
+    const float2* Kf = reinterpret_cast<const float2*>(S);
 #pragma unroll 4
-    for (int f = 0; f < F; ++f, Sf += a.n_pad, o += a.out_cols) {
+    for (int f = 0; f < F; ++f, Kf += a.n_pad, o += a.out_cols) {
       float v[4];
 #pragma unroll
       for (int c = 0; c < 4; ++c) {
-        const float s0 = Sf[lo_i[c]], s1 = Sf[lo_i[c] + 1];
-        v[c] = max_nan(min_nan(fmaf(s1 - s0, fr[c], s0), 1.0f), 0.0f);
+        const float2 k = Kf[lo_i[c]];
+        v[c] = __saturatef(fmaf(k.y, fr[c], k.x));   // FFMA.SAT: [0,1] like the reference
       }
       st_stream_f4(o, make_float4(v[0], v[1], v[2], v[3]));
+    }
+  }
+  // Rows poisoned by a NaN sample: torch.min/max propagate NaN, the whole row is NaN.  The
+  // saturating FFMA above flushed them to 0, so they are rewritten here (rare path).
+  if (rowflag[F]) {
+    const float qnan = __int_as_float(0x7fc00000);
+    for (int f = 0; f < F; ++f) {
+      if (!rowflag[f]) continue;
+      float* o = orow + (long long)f * a.out_cols;
+      for (int q = q0 + tid; q < q1; q += nthreads) st_stream_f4(o + 4 * q, make_float4(qnan, qnan, qnan, qnan));
     }
   }
 }
 
 // ------------------------------------------------------------------------------------- host
-static size_t stft_fixed_smem(int nperseg) {
+static size_t stft_fixed_smem(int nperseg, int threads, long long n_ends) {
   const int N = nperseg, P = N / 2, F = P + 1;
   const int LPF = P < 32 ? P : 32, FPW = 32 / LPF;
   size_t b = 0;
   b += sizeof(float2) * (P / 2 > 0 ? P / 2 : 1);
   b += sizeof(float2) * P;
-  b += sizeof(float2) * (kStftThreads / 32) * FPW * P;
-  b += sizeof(float2) * F;
+  b += sizeof(float2) * (threads / 32) * FPW * P;
+  b += sizeof(float2) * n_ends;
   b += sizeof(float) * N;
+  b += sizeof(int) * (F + 1 + ((F + 1) & 1));
   return b;
 }
 
@@ -334,23 +436,34 @@ static int check_pow2(int nperseg) {
 }
 
 struct StftLaunchShape {
-  int split, use_ws, n_pad;
+  int split, use_ws, n_pad, threads, ends_only, n_items;
   size_t smem, ws_per_cta;
   long long grid;
 };
 
-static StftLaunchShape stft_shape(long long rows, int nperseg, const eegspec_stft_plan& pl) {
+static StftLaunchShape stft_shape(long long rows, int nperseg, const eegspec_stft_plan& pl,
+                                  long long out_cols) {
   StftLaunchShape s;
   const int F = pl.n_freqs;
   s.n_pad = (int)(pl.n_slots | 1);
-  const size_t s_bytes = sizeof(float) * (size_t)F * s.n_pad;
-  const size_t fixed = stft_fixed_smem(nperseg);
+  s.ends_only = (!pl.gather && 2 * (pl.n_frames - 1) < out_cols &&
+                 out_cols * pl.n_frames < (1LL << 31)) ? 1 : 0;
+  s.n_items = s.ends_only ? (int)(2 * (pl.n_frames - 1)) : (int)out_cols;
+  const size_t s_bytes = sizeof(float2) * (size_t)F * s.n_pad;   // {value, delta} knot pairs
+  // 256-thread CTAs when four of them fit on an SM, otherwise 512 threads so that two CTAs
+  // still keep 32 warps resident.
+  s.threads = 256;
+  size_t fixed = stft_fixed_smem(nperseg, s.threads, s.ends_only ? s.n_items : 0);
+  if (fixed + s_bytes > 54 * 1024) {
+    s.threads = kStftMaxThreads;
+    fixed = stft_fixed_smem(nperseg, s.threads, s.ends_only ? s.n_items : 0);
+  }
   s.use_ws = (fixed + s_bytes > kSmemBudget) ? 1 : 0;
   s.smem = fixed + (s.use_ws ? 0 : s_bytes);
   s.ws_per_cta = s.use_ws ? s_bytes : 0;
   // Small batches: slice the columns of a row over several CTAs so that all 148 SMs write.
   int resident = (int)((220 * 1024) / (s.smem + 1024));
-  if (resident > 2048 / kStftThreads) resident = 2048 / kStftThreads;
+  if (resident > 1024 / s.threads) resident = 1024 / s.threads;   // 64 registers per thread
   if (resident < 1) resident = 1;
   const long long want = 148LL * resident;
   long long split = rows >= want ? 1 : (want + rows - 1) / rows;
@@ -365,12 +478,12 @@ size_t stft_image_workspace(long long rows, long long length, int nperseg, int n
   eegspec_stft_plan pl;
   if (stft_plan_make(length, nperseg, noverlap, out_cols, &pl) != EEGSPEC_OK) return 0;
   if (check_pow2(nperseg) != EEGSPEC_OK || rows <= 0) return 0;
-  const StftLaunchShape s = stft_shape(rows, nperseg, pl);
+  const StftLaunchShape s = stft_shape(rows, nperseg, pl, out_cols);
   return s.ws_per_cta * (size_t)s.grid;
 }
 
 template <int LOG2N, int MODE>
-static int launch_mode(const StftArgs& a, long long grid, size_t smem, cudaStream_t st) {
+static int launch_mode(const StftArgs& a, long long grid, size_t smem, int threads, cudaStream_t st) {
   static bool configured[64] = {};
   int dev = 0;
   cudaGetDevice(&dev);
@@ -381,27 +494,28 @@ static int launch_mode(const StftArgs& a, long long grid, size_t smem, cudaStrea
     if (e != cudaSuccess) return (int)e;
     configured[dev] = true;
   }
-  stft_image_kernel<LOG2N, MODE><<<(unsigned)grid, kStftThreads, smem, st>>>(a);
+  stft_image_kernel<LOG2N, MODE><<<(unsigned)grid, threads, smem, st>>>(a);
   count_launch();
   return (int)cudaGetLastError();
 }
 
 template <int LOG2N>
-static int launch_one(const StftArgs& a, long long grid, size_t smem, cudaStream_t st) {
-  if (a.logmag_only) return launch_mode<LOG2N, 2>(a, grid, smem, st);
-  if (a.use_ws) return launch_mode<LOG2N, 1>(a, grid, smem, st);
-  return launch_mode<LOG2N, 0>(a, grid, smem, st);
+static int launch_one(const StftArgs& a, long long grid, size_t smem, int threads, cudaStream_t st) {
+  if (a.logmag_only) return launch_mode<LOG2N, 2>(a, grid, smem, threads, st);
+  if (a.use_ws) return launch_mode<LOG2N, 1>(a, grid, smem, threads, st);
+  return launch_mode<LOG2N, 0>(a, grid, smem, threads, st);
 }
 
-static int dispatch(int nperseg, const StftArgs& a, long long grid, size_t smem, cudaStream_t st) {
+static int dispatch(int nperseg, const StftArgs& a, long long grid, size_t smem, int threads,
+                    cudaStream_t st) {
   switch (nperseg) {
-    case 16: return launch_one<4>(a, grid, smem, st);
-    case 32: return launch_one<5>(a, grid, smem, st);
-    case 64: return launch_one<6>(a, grid, smem, st);
-    case 128: return launch_one<7>(a, grid, smem, st);
-    case 256: return launch_one<8>(a, grid, smem, st);
-    case 512: return launch_one<9>(a, grid, smem, st);
-    case 1024: return launch_one<10>(a, grid, smem, st);
+    case 16: return launch_one<4>(a, grid, smem, threads, st);
+    case 32: return launch_one<5>(a, grid, smem, threads, st);
+    case 64: return launch_one<6>(a, grid, smem, threads, st);
+    case 128: return launch_one<7>(a, grid, smem, threads, st);
+    case 256: return launch_one<8>(a, grid, smem, threads, st);
+    case 512: return launch_one<9>(a, grid, smem, threads, st);
+    case 1024: return launch_one<10>(a, grid, smem, threads, st);
     default: return EEGSPEC_EUNSUPPORTED;
   }
 }
@@ -417,7 +531,7 @@ int stft_image_launch(const float* x, long long rows, long long length, long lon
   if (rc != EEGSPEC_OK) return rc;
   if ((rc = check_pow2(nperseg)) != EEGSPEC_OK) return rc;
   if (rows > (1LL << 27)) return EEGSPEC_EUNSUPPORTED;
-  const StftLaunchShape s = stft_shape(rows, nperseg, pl);
+  const StftLaunchShape s = stft_shape(rows, nperseg, pl, out_cols);
   if (s.use_ws) {
     if (!workspace || workspace_bytes < s.ws_per_cta * (size_t)s.grid) return EEGSPEC_EWORKSPACE;
     if (reinterpret_cast<uintptr_t>(workspace) & 15) return EEGSPEC_EALIGN;
@@ -443,10 +557,14 @@ int stft_image_launch(const float* x, long long rows, long long length, long lon
   a.D = (int)out_cols - 1;
   a.q_step = (pl.n_frames - 1) / a.D;
   a.r_step = (int)((pl.n_frames - 1) % a.D);
+  a.q32_step = (32 * (pl.n_frames - 1)) / a.D;
+  a.r32_step = (int)((32 * (pl.n_frames - 1)) % a.D);
+  a.ends_only = s.ends_only;
+  a.n_items = s.n_items;
   a.small_index = ((double)out_cols * (double)pl.n_frames < 4.0e9) ? 1 : 0;
   a.inv_d = 1.0f / (float)a.D;
   a.eps = eps;
-  return dispatch(nperseg, a, s.grid, s.smem, st);
+  return dispatch(nperseg, a, s.grid, s.smem, s.threads, st);
 }
 
 int stft_logmag_launch(const float* x, long long rows, long long length, long long row_stride,
@@ -473,7 +591,7 @@ int stft_logmag_launch(const float* x, long long rows, long long length, long lo
   a.out_cols = 4;
   a.D = 3;
   a.inv_d = 1.f / 3.f;
-  return dispatch(nperseg, a, rows, stft_fixed_smem(nperseg), st);
+  return dispatch(nperseg, a, rows, stft_fixed_smem(nperseg, 256, 0), 256, st);
 }
 
 }  // namespace eegspec
