@@ -81,7 +81,10 @@ __device__ __forceinline__ void fft_phase(const StftArgs& a, const float* __rest
     for (int s = 0; s < NSH; ++s) {
       const int h = (P / 2) >> s;
       h_tw[s] = (le & h) ? tw[(le % h) * (P / (2 * h))] : make_float2(1.f, 0.f);
+      // opaque to the optimiser: keeps the twiddles in registers instead of re-deriving them per frame
+      asm volatile("" : "+f"(h_tw[s].x), "+f"(h_tw[s].y));
     }
+    asm volatile("" : "+f"(h_win.x), "+f"(h_win.y), "+f"(h_utw.x), "+f"(h_utw.y));
   }
 
   // Per-lane output rows (k = le + LPF*r) are loop invariant: hoist their base pointers.
@@ -91,28 +94,21 @@ __device__ __forceinline__ void fft_phase(const StftArgs& a, const float* __rest
   float* Snyq = S + (long long)P * a.n_pad * STRIDE;
   const bool small = a.L < (1LL << 30) && !a.gather;   // 32-bit sample indices
 
-  // Sample fetch for one slot: two values per complex point, zero outside [0, L).
+  // Sample fetch for one slot: two values per complex point, zero outside [0, L) (SciPy's zero
+  // boundary extension and end padding).  Unsigned compares fold the two range checks into one.
+  const int lane_off = 2 * le * NPL - a.half;
   auto fetch = [&](int slot, float (&v0)[NPL], float (&v1)[NPL]) {
-    const bool live = slot < a.n_slots;
     if (small) {
-      const int s0 = slot * a.hop - a.half;
-      const int len = (int)a.L;
-      if (live && s0 >= 0 && s0 + N <= len) {
+      const int s0 = slot * a.hop + lane_off;
+      const unsigned len = slot < a.n_slots ? (unsigned)a.L : 0u;
 #pragma unroll
-        for (int r = 0; r < NPL; ++r) {
-          const int i0 = s0 + 2 * (le * NPL + r);
-          v0[r] = __ldg(xrow + i0);
-          v1[r] = __ldg(xrow + i0 + 1);
-        }
-      } else {
-#pragma unroll
-        for (int r = 0; r < NPL; ++r) {
-          const int i0 = s0 + 2 * (le * NPL + r), i1 = i0 + 1;
-          v0[r] = (live && i0 >= 0 && i0 < len) ? __ldg(xrow + i0) : 0.f;
-          v1[r] = (live && i1 >= 0 && i1 < len) ? __ldg(xrow + i1) : 0.f;
-        }
+      for (int r = 0; r < NPL; ++r) {
+        const int i0 = s0 + 2 * r;
+        v0[r] = (unsigned)i0 < len ? __ldg(xrow + i0) : 0.f;
+        v1[r] = (unsigned)(i0 + 1) < len ? __ldg(xrow + i0 + 1) : 0.f;
       }
     } else {
+      const bool live = slot < a.n_slots;
       long long frame = slot;
       if (a.gather) {
         int rem;
@@ -144,7 +140,7 @@ __device__ __forceinline__ void fft_phase(const StftArgs& a, const float* __rest
       z[r] = make_float2(nv0[r] * w.x, nv1[r] * w.y);
     }
     // Software pipeline: the next frame's samples are in flight while this one is transformed.
-    if (base + stride_slots < a.n_slots) fetch(slot + stride_slots, nv0, nv1);
+    fetch(slot + stride_slots, nv0, nv1);   // out-of-range slots read as zeros
 
     // Decimation-in-frequency radix-2; element e ends up holding Z[bitrev(e)].
 #pragma unroll
@@ -231,7 +227,7 @@ stft_image_kernel(const StftArgs a) {
   float2* tw = reinterpret_cast<float2*>(smem_raw);                 // P/2 (>=1)
   float2* utw = tw + (P / 2 > 0 ? P / 2 : 1);                       // P
   float2* zs = utw + P;                                             // warps * FPW * P
-  float2* ends = zs + nwarps * FPW * P;                             // n_items when ends_only
+  float2* ends = zs + nwarps * FPW * P;                             // one per segment when ends_only
   float* win = reinterpret_cast<float*>(ends + (a.ends_only ? a.n_items : 0));  // N
   int* rowflag = reinterpret_cast<int*>(win + N);                   // F + 1 (NaN rows, any)
   float* S_sm = reinterpret_cast<float*>(rowflag + F + 1 + ((F + 1) & 1));      // F*n_pad*STRIDE
@@ -274,8 +270,7 @@ stft_image_kernel(const StftArgs a) {
           const int jn = q + (r ? 1 : 0);               // first column of seg + 1
           const int jl = (seg == nm1 - 1) ? D : jn - 1; // last column of seg
           // column j sits at fraction (j*nm1 - seg*D)/D inside segment seg
-          ends[2 * seg] = make_float2(__int_as_float(seg * STRIDE), (float)(jf * nm1 - seg * D) * a.inv_d);
-          ends[2 * seg + 1] = make_float2(__int_as_float(seg * STRIDE), (float)(jl * nm1 - seg * D) * a.inv_d);
+          ends[seg] = make_float2((float)(jf * nm1 - seg * D) * a.inv_d, (float)(jl * nm1 - seg * D) * a.inv_d);
           jf = jn;
         }
       }
@@ -300,13 +295,12 @@ stft_image_kernel(const StftArgs a) {
     float* Sf = S + (long long)f * a.n_pad * STRIDE;
     float lo = __int_as_float(0x7f800000), hi = __int_as_float(0xff800000);
     if (a.ends_only) {
-      for (int t = lane; t < a.n_items; t += 32) {
-        const float2 e = ends[t];
-        const int o = __float_as_int(e.x);
-        const float s0 = Sf[o], s1 = Sf[o + STRIDE];
-        const float v = fmaf(s1 - s0, e.y, s0);
-        lo = min_nan(lo, v);
-        hi = max_nan(hi, v);
+      for (int seg = lane; seg < a.n_items; seg += 32) {   // n_items = segments here
+        const float2 e = ends[seg];                          // fractions of first / last column
+        const float s0 = Sf[seg * STRIDE], d = Sf[(seg + 1) * STRIDE] - s0;
+        const float va = fmaf(d, e.x, s0), vb = fmaf(d, e.y, s0);
+        lo = min_nan(lo, min_nan(va, vb));
+        hi = max_nan(hi, max_nan(va, vb));
       }
     } else {
       long long i;
@@ -448,7 +442,7 @@ static StftLaunchShape stft_shape(long long rows, int nperseg, const eegspec_stf
   s.n_pad = (int)(pl.n_slots | 1);
   s.ends_only = (!pl.gather && 2 * (pl.n_frames - 1) < out_cols &&
                  out_cols * pl.n_frames < (1LL << 31)) ? 1 : 0;
-  s.n_items = s.ends_only ? (int)(2 * (pl.n_frames - 1)) : (int)out_cols;
+  s.n_items = s.ends_only ? (int)(pl.n_frames - 1) : (int)out_cols;   // segments | columns
   const size_t s_bytes = sizeof(float2) * (size_t)F * s.n_pad;   // {value, delta} knot pairs
   // 256-thread CTAs when four of them fit on an SM, otherwise 512 threads so that two CTAs
   // still keep 32 warps resident.
