@@ -21,52 +21,9 @@
 #include <mutex>
 #include <vector>
 
-#include "common.cuh"
-#include "internal.h"
+#include "melspec_common.cuh"
 
 namespace eegspec {
-
-constexpr int kFold = 64;       // win_length / 2
-constexpr int kBinGroups = 8;   // one warp per bin group
-constexpr int kBinsPerGroup = 13;
-constexpr int kBinSlots = kBinGroups * kBinsPerGroup;  // 104 >= bins with mel weight
-constexpr int kGroupPitch = 16;                        // table row pitch per group (float4 x 4)
-constexpr int kTileFrames = 128;
-constexpr int kMelThreads = 256;
-constexpr int kMaxMels = 256;
-constexpr int kMaxCrop = 12288;
-
-struct MelTables {            // device-resident constant tables for one parameter set
-  float* cos_t;               // [kFold][kBinGroups][kGroupPitch]
-  float* sin_t;
-  float* win_half;            // [kFold]  w[W/2 + m]
-  int* mel_k0;                // [n_mels] first tap, as a bin slot (bin - k_lo)
-  float* mel_w0;              // [n_mels]
-  float* mel_w1;              // [n_mels]
-};
-
-struct MelArgs {
-  const float* eeg;
-  float* q;       // [batch][pairs][n_mels][n_time]  10 log10(max(amin, mel))
-  float* refdb;   // [batch][pairs]                  10 log10(max(amin, max mel))
-  float* out;     // [batch][n_mels][n_time][n_chains]
-  MelTables t;
-  long long rec_stride, ch_stride, t_stride, length;
-  int crop, crop_off, hop, n_frames, n_time, n_mels, n_pairs, n_chains, ppc, pad_mode;
-  float amin, top_db, db_offset, inv_db_scale;
-  int pair_a[EEGSPEC_MAX_PAIRS], pair_b[EEGSPEC_MAX_PAIRS];
-};
-
-__device__ __forceinline__ float padded_sample(const float* y, int i, int n, int pad_mode) {
-  if (i < 0) {
-    if (pad_mode == 0) return 0.f;
-    i = -i;
-  } else if (i >= n) {
-    if (pad_mode == 0) return 0.f;
-    i = 2 * (n - 1) - i;
-  }
-  return (i >= 0 && i < n) ? y[i] : 0.f;
-}
 
 __global__ void __launch_bounds__(kMelThreads, 1) melspec_pair_kernel(const MelArgs a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -330,6 +287,7 @@ struct MelHostTables {
   MelGeometry g;
   std::vector<float> cos_t, sin_t, win_half, w0, w1;
   std::vector<int> k0;
+  std::vector<unsigned short> tc_tab;
 };
 
 static int validate(const eegspec_mel_params* p) {
@@ -344,7 +302,7 @@ static int validate(const eegspec_mel_params* p) {
   if (p->win_length != 2 * kFold || p->n_fft < p->win_length) return EEGSPEC_EUNSUPPORTED;
   if (p->n_mels > kMaxMels || p->crop > kMaxCrop || p->crop < p->win_length) return EEGSPEC_EUNSUPPORTED;
   if (p->pad_mode != 0 && p->pad_mode != 1) return EEGSPEC_EUNSUPPORTED;
-  if (p->engine < 0 || p->engine > 1) return EEGSPEC_EUNSUPPORTED;
+  if (p->engine < 0 || p->engine > 2) return EEGSPEC_EUNSUPPORTED;
   return EEGSPEC_OK;
 }
 
@@ -399,6 +357,18 @@ static int build_host_tables(const eegspec_mel_params& p, MelHostTables& h) {
   h.win_half.assign(kFold, 0.f);
   for (int m = 0; m < kFold; ++m)
     h.win_half[m] = (float)(0.5 - 0.5 * cos(2.0 * M_PI * (kFold + m) / (2.0 * kFold)));
+  {  // engine 2: the same tables as [bin slot][m] doubles, split into fp16 halves
+    const int nb_used = k_hi - k_lo + 1;
+    std::vector<double> cd((size_t)nb_used * kFold), sd((size_t)nb_used * kFold);
+    for (int ks = 0; ks < nb_used; ++ks)
+      for (int m = 0; m < kFold; ++m) {
+        const long long km = ((long long)(k_lo + ks) * m) % p.n_fft;
+        cd[(size_t)ks * kFold + m] = cos(theta * km);
+        sd[(size_t)ks * kFold + m] = sin(theta * km);
+      }
+    h.tc_tab.assign(kTcTableHalves, 0);
+    melspec_tc_build_tables(cd.data(), sd.data(), nb_used, h.tc_tab.data());
+  }
   return EEGSPEC_OK;
 }
 
@@ -453,6 +423,7 @@ static int device_tables(const eegspec_mel_params& p, MelTables* out, MelGeometr
   if ((ce = upload(&e.dev.mel_k0, h.k0)) != cudaSuccess) return (int)ce;
   if ((ce = upload(&e.dev.mel_w0, h.w0)) != cudaSuccess) return (int)ce;
   if ((ce = upload(&e.dev.mel_w1, h.w1)) != cudaSuccess) return (int)ce;
+  if ((ce = upload(&e.dev.tc_tab, h.tc_tab)) != cudaSuccess) return (int)ce;
   g_tables.push_back(e);
   *out = e.dev;
   return EEGSPEC_OK;
@@ -546,9 +517,16 @@ int melspec_launch(const float* eeg, long long batch, int n_ch, long long length
     a.q = static_cast<float*>(workspace);
     a.refdb = reinterpret_cast<float*>(static_cast<char*>(workspace) + q_bytes);
     a.out = out + r0 * (long long)p->n_mels * g.n_time * p->n_chains;
-    melspec_pair_kernel<<<dim3(n_pairs, (unsigned)nb), kMelThreads, smem, st>>>(a);
-    count_launch();
-    cudaError_t e = cudaGetLastError();
+    cudaError_t e;
+    if (p->engine == 1) {
+      melspec_pair_kernel<<<dim3(n_pairs, (unsigned)nb), kMelThreads, smem, st>>>(a);
+      count_launch();
+      e = cudaGetLastError();
+    } else {   // default: tcgen05 engine
+      const int rc2 = melspec_tc_launch_pair(a, n_pairs, nb, st);
+      if (rc2 < 0) return rc2;
+      e = static_cast<cudaError_t>(rc2);
+    }
     if (e != cudaSuccess) return (int)e;
     const long long n_pix = nb * p->n_mels * g.n_time;
     melspec_combine_kernel<<<(unsigned)((n_pix + 255) / 256), 256, 0, st>>>(a, n_pix);

@@ -22,24 +22,48 @@ def run(x, **kw):
     return y.cpu().numpy()
 
 
+ENGINES = [pytest.param(2, id="tcgen05"), pytest.param(1, id="simt")]   # 0 (default) == 2
+
+
+@pytest.mark.parametrize("engine", ENGINES)
 @pytest.mark.parametrize("case,key,mode", [("clean", "y", "constant"), ("clean", "y_reflect", "reflect"),
                                             ("nan", "y", "constant"), ("range", "y", "constant")])
-def test_against_golden(melspec_golden, case, key, mode):
+def test_against_golden(melspec_golden, case, key, mode, engine):
     want = melspec_golden[f"{case}/{key}"]
-    got = run(melspec_golden[f"{case}/x"], pad_mode=mode)
+    got = run(melspec_golden[f"{case}/x"], pad_mode=mode, engine=engine)
     assert got.shape == want.shape == (1, 128, 256, 4) and got.dtype == np.float32
     err = np.abs(got - want).max()
     assert err <= ATOL, f"{case}/{mode}: max abs err {err:.3e}"
 
 
-def test_against_oracle_batch():
+@pytest.mark.parametrize("engine", ENGINES)
+def test_against_oracle_batch(engine):
     rng = np.random.default_rng(21)
     x = eeg_like(rng, (5, 20, 10000))
     want = mo.eeg_to_spectrogram_batch_oracle(x[:3])
-    got = run(x)
+    got = run(x, engine=engine)
     assert got.shape == (5, 128, 256, 4)
     err = np.abs(got[:3] - want).max()
     assert err <= ATOL, f"max abs err {err:.3e}"
+
+
+@pytest.mark.parametrize("scale", [1e-6, 1e-3, 1.0, 1e3, 1e6])
+def test_tensor_core_engine_is_scale_invariant(scale):
+    """The fp16 operand split is protected by an exact power-of-two pre-scale: amplitudes from
+    nanovolts to volts give the image the oracle gives (dB referencing removes the scale)."""
+    rng = np.random.default_rng(26)
+    x = eeg_like(rng, (1, 20, 10000)) * np.float32(scale)
+    want = mo.eeg_to_spectrogram_batch_oracle(x)
+    for engine in (2, 1):
+        err = np.abs(run(x, engine=engine) - want).max()
+        assert err <= ATOL, f"engine {engine} scale {scale}: max abs err {err:.3e}"
+
+
+def test_engines_agree_at_size():
+    rng = np.random.default_rng(27)
+    x = eeg_like(rng, (40, 20, 10000))
+    a, b = run(x, engine=2), run(x, engine=1)
+    assert np.abs(a - b).max() <= 2e-4
 
 
 def test_single_record_time_major_and_crop():
