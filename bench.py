@@ -263,11 +263,11 @@ def main():
     achieved_n = RECORDS * BYTES_N / per_launch_s / 1e9
     roofline = {
         "bound": "hbm", "achieved": achieved_n, "peak": peak, "unit": "GB/s", "frac": achieved_n / peak,
-        "traffic": melspec_step_traffic(),
+        "traffic": committed_traffic("melspec_chain_dram_bytes_per_step"),
         "peak_source": peak_src,
-        "kernel": "melspec_pair_kernel + melspec_combine_kernel (all launches of one step; "
-                  "algorithmic bytes 1 324 288 B/record x 1024 records per step)",
-        "note": "fp32 SIMT pruned-DFT engine is FFMA-bound, not HBM-bound (DESIGN.md)",
+        "kernel": "melspec_chain_kernel (engine 3: one persistent clustered launch per step; "
+                  "algorithmic bytes 1 324 288 B/record x 1024 records per launch)",
+        "note": "co-bound by issue slots / MUFU / tensor pipe, not by HBM alone (DESIGN.md 3.2)",
     }
     del keep["n"]
 

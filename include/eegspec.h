@@ -109,7 +109,8 @@ typedef struct eegspec_mel_params {
   int32_t pair_a[EEGSPEC_MAX_PAIRS]; /* channel index of the minuend, chain-major        */
   int32_t pair_b[EEGSPEC_MAX_PAIRS]; /* channel index of the subtrahend                  */
   int32_t time_major;    /* 0: record is (n_ch, L) channel-major; 1: (L, n_ch)           */
-  int32_t engine;        /* 0 = default (= 2), 1 = fp32 SIMT DFT, 2 = tcgen05 split-fp16 DFT */
+  int32_t engine;        /* 0 = default (3 when the geometry allows, else 2), 1 = fp32 SIMT DFT,
+                          * 2 = tcgen05 DFT + scratch, 3 = persistent clustered tcgen05, no scratch */
 } eegspec_mel_params;
 
 /* Fills the defaults above (HMS montage LL, LP, RP, RR in EEG_COLUMNS order). */

@@ -287,7 +287,8 @@ struct MelHostTables {
   MelGeometry g;
   std::vector<float> cos_t, sin_t, win_half, w0, w1;
   std::vector<int> k0;
-  std::vector<unsigned short> tc_tab;
+  std::vector<unsigned short> tc_tab, tc3_tab;
+  bool chain_ok = false;
 };
 
 static int validate(const eegspec_mel_params* p) {
@@ -302,19 +303,27 @@ static int validate(const eegspec_mel_params* p) {
   if (p->win_length != 2 * kFold || p->n_fft < p->win_length) return EEGSPEC_EUNSUPPORTED;
   if (p->n_mels > kMaxMels || p->crop > kMaxCrop || p->crop < p->win_length) return EEGSPEC_EUNSUPPORTED;
   if (p->pad_mode != 0 && p->pad_mode != 1) return EEGSPEC_EUNSUPPORTED;
-  if (p->engine < 0 || p->engine > 2) return EEGSPEC_EUNSUPPORTED;
+  if (p->engine < 0 || p->engine > 3) return EEGSPEC_EUNSUPPORTED;
+  return EEGSPEC_OK;
+}
+
+// Frame geometry only (cheap: runs on every call; the filter bank is built once per parameter set).
+static int frame_geometry(const eegspec_mel_params& p, MelGeometry& g) {
+  const int hop = p.hop > 0 ? p.hop : p.crop / p.n_time_div;
+  if (hop <= 0) return EEGSPEC_EINVAL;
+  g.hop = hop;
+  g.n_frames = 1 + p.crop / hop;  // centred: 1 + (crop + n_fft - n_fft)//hop
+  g.n_time = (g.n_frames / 32) * 32;
+  g.n_pairs = p.n_chains * p.pairs_per_chain;
+  g.k_lo = g.k_hi = 0;
+  if (g.n_time <= 0) return EEGSPEC_ESHORT;
+  if (g.n_frames - g.n_time > 2 * kFold * kTileFrames / kBinSlots) return EEGSPEC_EUNSUPPORTED;
   return EEGSPEC_OK;
 }
 
 static int build_host_tables(const eegspec_mel_params& p, MelHostTables& h) {
-  const int hop = p.hop > 0 ? p.hop : p.crop / p.n_time_div;
-  if (hop <= 0) return EEGSPEC_EINVAL;
-  h.g.hop = hop;
-  h.g.n_frames = 1 + p.crop / hop;  // centred: 1 + (crop + n_fft - n_fft)//hop
-  h.g.n_time = (h.g.n_frames / 32) * 32;
-  h.g.n_pairs = p.n_chains * p.pairs_per_chain;
-  if (h.g.n_time <= 0) return EEGSPEC_ESHORT;
-  if (h.g.n_frames - h.g.n_time > 2 * kFold * kTileFrames / kBinSlots) return EEGSPEC_EUNSUPPORTED;
+  const int grc = frame_geometry(p, h.g);
+  if (grc != EEGSPEC_OK) return grc;
 
   std::vector<float> fb;
   slaney_filterbank(p, fb);
@@ -368,6 +377,16 @@ static int build_host_tables(const eegspec_mel_params& p, MelHostTables& h) {
       }
     h.tc_tab.assign(kTcTableHalves, 0);
     melspec_tc_build_tables(cd.data(), sd.data(), nb_used, h.tc_tab.data());
+    // engine 3 folds the window into the tables; E[0] = y[c] + y[c] is halved there
+    for (int ks = 0; ks < nb_used; ++ks)
+      for (int m = 0; m < kFold; ++m) {
+        const double w = (0.5 - 0.5 * cos(2.0 * M_PI * (kFold + m) / (2.0 * kFold))) * (m == 0 ? 0.5 : 1.0);
+        cd[(size_t)ks * kFold + m] *= w;
+        sd[(size_t)ks * kFold + m] *= w;
+      }
+    h.tc3_tab.assign(kTcTableHalves, 0);
+    melspec_tc_build_tables(cd.data(), sd.data(), nb_used, h.tc3_tab.data());
+    h.chain_ok = melspec_chain_bank_matches(p, k_lo, h.k0.data(), h.w0.data(), h.w1.data());
   }
   return EEGSPEC_OK;
 }
@@ -375,9 +394,9 @@ static int build_host_tables(const eegspec_mel_params& p, MelHostTables& h) {
 int melspec_geometry(const eegspec_mel_params* p, MelGeometry* g) {
   int rc = validate(p);
   if (rc != EEGSPEC_OK) return rc;
-  MelHostTables h;
-  rc = build_host_tables(*p, h);
-  if (rc == EEGSPEC_OK && g) *g = h.g;
+  MelGeometry tmp;
+  rc = frame_geometry(*p, tmp);
+  if (rc == EEGSPEC_OK && g) *g = tmp;
   return rc;
 }
 
@@ -389,7 +408,7 @@ struct TableKey {
            n_mels == o.n_mels && fmin == o.fmin && fmax == o.fmax;
   }
 };
-struct TableEntry { TableKey key; MelTables dev; MelGeometry g; };
+struct TableEntry { TableKey key; MelTables dev; MelGeometry g; bool chain_ok; };
 
 static std::mutex g_table_mu;
 static std::vector<TableEntry> g_tables;
@@ -402,18 +421,26 @@ static cudaError_t upload(T** dst, const std::vector<T>& src) {
 }
 
 // Device tables for (device, filterbank parameters); built once, kept for the process lifetime.
-static int device_tables(const eegspec_mel_params& p, MelTables* out, MelGeometry* g) {
+static int device_tables(const eegspec_mel_params& p, MelTables* out, MelGeometry* g, bool* chain_ok) {
   int dev = 0;
   cudaError_t ce = cudaGetDevice(&dev);
   if (ce != cudaSuccess) return (int)ce;
-  MelHostTables h;
-  int rc = build_host_tables(p, h);
+  int rc = frame_geometry(p, *g);
   if (rc != EEGSPEC_OK) return rc;
-  *g = h.g;
   const TableKey key{dev, p.sr, p.n_fft, p.win_length, p.n_mels, p.fmin, p.fmax};
   std::lock_guard<std::mutex> lock(g_table_mu);
   for (const TableEntry& e : g_tables)
-    if (e.key == key) { *out = e.dev; return EEGSPEC_OK; }
+    if (e.key == key) {
+      *out = e.dev;
+      *chain_ok = e.chain_ok;
+      g->k_lo = e.g.k_lo;
+      g->k_hi = e.g.k_hi;
+      return EEGSPEC_OK;
+    }
+  MelHostTables h;   // first use of this bank on this device: build and upload (milliseconds)
+  if ((rc = build_host_tables(p, h)) != EEGSPEC_OK) return rc;
+  *g = h.g;
+  *chain_ok = h.chain_ok;
   TableEntry e;
   e.key = key;
   e.g = h.g;
@@ -424,6 +451,8 @@ static int device_tables(const eegspec_mel_params& p, MelTables* out, MelGeometr
   if ((ce = upload(&e.dev.mel_w0, h.w0)) != cudaSuccess) return (int)ce;
   if ((ce = upload(&e.dev.mel_w1, h.w1)) != cudaSuccess) return (int)ce;
   if ((ce = upload(&e.dev.tc_tab, h.tc_tab)) != cudaSuccess) return (int)ce;
+  if ((ce = upload(&e.dev.tc3_tab, h.tc3_tab)) != cudaSuccess) return (int)ce;
+  e.chain_ok = h.chain_ok;
   g_tables.push_back(e);
   *out = e.dev;
   return EEGSPEC_OK;
@@ -469,12 +498,8 @@ int melspec_launch(const float* eeg, long long batch, int n_ch, long long length
 
   MelArgs a;
   MelGeometry g;
-  if ((rc = device_tables(*p, &a.t, &g)) != EEGSPEC_OK) return rc;
-  const long long chunk = batch < kMelChunk ? batch : kMelChunk;
-  const size_t need = per_record_scratch(*p, g) * (size_t)chunk;
-  if (!workspace || workspace_bytes < need) return EEGSPEC_EWORKSPACE;
-  if (reinterpret_cast<uintptr_t>(workspace) & 15) return EEGSPEC_EALIGN;
-
+  bool chain_ok = false;
+  if ((rc = device_tables(*p, &a.t, &g, &chain_ok)) != EEGSPEC_OK) return rc;
   a.rec_stride = rec_stride;
   a.ch_stride = p->time_major ? 1 : length;
   a.t_stride = p->time_major ? n_ch : 1;
@@ -497,6 +522,21 @@ int melspec_launch(const float* eeg, long long batch, int n_ch, long long length
     a.pair_a[i] = i < n_pairs ? p->pair_a[i] : 0;
     a.pair_b[i] = i < n_pairs ? p->pair_b[i] : 0;
   }
+
+  // Engine 3 (default when the geometry is the north-star one): one persistent launch, no scratch.
+  if (p->engine == 0 || p->engine == 3) {
+    a.eeg = eeg;
+    a.out = out;
+    a.q = nullptr;
+    a.refdb = nullptr;
+    const int rc3 = chain_ok ? melspec_chain_launch(a, *p, batch, st) : EEGSPEC_EUNSUPPORTED;
+    if (rc3 != EEGSPEC_EUNSUPPORTED || p->engine == 3) return rc3;
+  }
+
+  const long long chunk = batch < kMelChunk ? batch : kMelChunk;
+  const size_t need = per_record_scratch(*p, g) * (size_t)chunk;
+  if (!workspace || workspace_bytes < need) return EEGSPEC_EWORKSPACE;
+  if (reinterpret_cast<uintptr_t>(workspace) & 15) return EEGSPEC_EALIGN;
 
   static bool configured[64] = {};
   int dev = 0;
@@ -522,7 +562,7 @@ int melspec_launch(const float* eeg, long long batch, int n_ch, long long length
       melspec_pair_kernel<<<dim3(n_pairs, (unsigned)nb), kMelThreads, smem, st>>>(a);
       count_launch();
       e = cudaGetLastError();
-    } else {   // default: tcgen05 engine
+    } else {   // tcgen05 engine with scratch
       const int rc2 = melspec_tc_launch_pair(a, n_pairs, nb, st);
       if (rc2 < 0) return rc2;
       e = static_cast<cudaError_t>(rc2);

@@ -1,0 +1,654 @@
+// Mode N, engine 3: persistent, clustered, scratch-free montage -> mel image kernel.
+//
+// Same arithmetic as engine 2 (melspec_tc.cu: folded 128-sample Hann frame -> pruned DFT on
+// tcgen05 with split-fp16 operands and fp32 TMEM accumulators -> |X|^2 -> 2-tap mel -> dB), but
+//   * a work item is (record, chain); a cluster of two CTAs owns it, CTA h taking frames
+//     128h .. 128h+127 of each of the chain's pairs (one M = 128 MMA tile per pair);
+//   * every thread owns one frame (one TMEM lane) and 64 mels and keeps the chain sum acc[64]
+//     and the previous pair's log-mel values qprev[64] in registers; the mel taps are literals
+//     (mel_default_epilogue.h, generated) so that all register indices are static;
+//   * power_to_db(ref = max) needs the pair maximum over both halves: the two CTAs exchange it
+//     through distributed shared memory and the fold of pair p is deferred to the epilogue of
+//     pair p+1, so the exchange latency is never on the critical path;
+//   * the epilogue of tile j-1 runs while the tensor pipe works on tile j (accumulators are
+//     double-buffered in TMEM), and the next pair's electrode rows arrive by cp.async.bulk.
+// No scratch, no second kernel: the image is written once, from registers.
+//
+// Front half follows the reference (pair list /root/reference/root/config/config.yml:529-545,
+// differencing /root/reference/root/src/utils/data_utils.py:183-215, crop
+// /root/reference/root/src/utils/cfg_utils.py:369-371, NaN fill cfg_utils.py:380-385).
+#include <cuda_fp16.h>
+
+#include "mel_default_epilogue.h"
+#include "melspec_common.cuh"
+
+namespace eegspec {
+
+constexpr int kCThreads = 256;
+constexpr int kCBins = 112;                         // MMA N
+constexpr int kCTabBytes = kCBins * kFold * 2;      // 14 336
+constexpr int kCTileBytes = kTileFrames * kFold * 2;  // 16 384
+constexpr int kCMargin = 64;                        // padding samples either side of y
+constexpr int kCStageFloats = 5376;                 // one staged electrode row segment
+constexpr int kCYFloats = kCStageFloats + 2 * kCMargin + 128;
+constexpr int kCMaxExtra = 4;                       // frames beyond the kept width (max only)
+constexpr int kCAccCols = 2 * kCBins;               // Re | Im
+constexpr int kCXCols = 16;                         // MMA N of the extra-frame product
+constexpr int kCXTileBytes = kCXCols * kFold * 2;   // 2 048: 16 rows x 64 fp16
+constexpr int kCXTmemCol = 2 * kCAccCols;           // 448: [buffer][Re | Im][16] in the spare columns
+constexpr float kLog2To10Log10 = 3.0102999566398120f;
+
+struct ChainArgs {
+  const float* eeg;
+  float* out;
+  const unsigned short* tab;   // window-folded fp16 {cos hi, cos lo, sin hi, sin lo}, UMMA layout
+  const int* mel_k0;           // runtime taps, used for the extra frames only
+  const float* mel_w0;
+  const float* mel_w1;
+  long long rec_stride, ch_stride;
+  long long n_items;           // batch * n_chains
+  int crop, crop_off, hop, n_frames, n_mels, n_time, n_chains, ppc, pad_mode;
+  int seg_lo[2], seg_n[2];     // staged sample range of each half (multiples of 4)
+  float log2_amin, top_log2, out_bias, out_gain;
+  int pair_a[EEGSPEC_MAX_PAIRS], pair_b[EEGSPEC_MAX_PAIRS];
+};
+
+// ------------------------------------------------------------------------------ PTX helpers
+__device__ __forceinline__ uint32_t c_smem_u32(const void* p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ uint64_t c_umma_desc(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr >> 4) & 0x3FFF);
+  d |= (uint64_t)(128 >> 4) << 16;   // LBO: next K core matrix
+  d |= (uint64_t)(1024 >> 4) << 32;  // SBO: next 8-row group
+  d |= (uint64_t)1 << 46;            // sm_100 descriptor version
+  return d;
+}
+__host__ __device__ constexpr int c_umma_offset(int row, int k) {
+  return (row >> 3) * 1024 + (k >> 3) * 128 + (row & 7) * 16 + (k & 7) * 2;
+}
+constexpr uint32_t kCIdesc = (1u << 4) | ((uint32_t)(kCBins >> 3) << 17) | ((uint32_t)(kTileFrames >> 4) << 24);
+// extra frames: D'[bin][frame] = table (A, M = 128 rows of which 112 are table) x frames (B, N = 16)
+constexpr uint32_t kCIdescX = (1u << 4) | ((uint32_t)(kCXCols >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+
+__device__ __forceinline__ void c_umma(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t acc,
+                                       uint32_t idesc = kCIdesc) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}\n"
+      :
+      : "r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(acc)
+      : "memory");
+}
+// 4 TMEM columns of this thread's lane.
+__device__ __forceinline__ void c_tmem_ld4(uint32_t addr, float (&v)[4]) {
+  uint32_t a[4];
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0, %1, %2, %3}, [%4];\n"
+               : "=r"(a[0]), "=r"(a[1]), "=r"(a[2]), "=r"(a[3])
+               : "r"(addr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;\n" : "+r"(a[0]), "+r"(a[1]), "+r"(a[2]), "+r"(a[3]) : : "memory");
+#pragma unroll
+  for (int i = 0; i < 4; ++i) v[i] = __uint_as_float(a[i]);
+}
+__device__ __forceinline__ void c_mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void c_mbar_wait(uint32_t bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t.reg .pred P1;\n\t"
+      "CW_%=:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n\t"
+      "@!P1 bra CW_%=;\n\t}\n"
+      :
+      : "r"(bar), "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ void c_mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+// 1-D bulk copy global -> shared, completion counted on an mbarrier (TMA engine).
+__device__ __forceinline__ void c_bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+               "l"(src), "r"(bytes), "r"(bar)
+               : "memory");
+}
+__device__ __forceinline__ uint32_t c_cluster_rank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void c_cluster_arrive() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void c_cluster_arrive_relaxed() {
+  asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void c_cluster_wait() {
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void c_st_peer_f32(uint32_t local_addr, uint32_t peer_rank, float v) {
+  uint32_t remote;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local_addr), "r"(peer_rank));
+  asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(remote), "f"(v) : "memory");
+}
+__device__ __forceinline__ float c_lg2(float x) {
+  float r;
+  asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+// 16 TMEM columns of this thread's lane for Re and for Im, and the wait that makes them valid.
+__device__ __forceinline__ void c_tmem_ld16x2(uint32_t addr_re, uint32_t addr_im, float (&re)[16], float (&im)[16]) {
+  uint32_t a[16], b[16];
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];\n"
+      : "=r"(a[0]), "=r"(a[1]), "=r"(a[2]), "=r"(a[3]), "=r"(a[4]), "=r"(a[5]), "=r"(a[6]), "=r"(a[7]), "=r"(a[8]),
+        "=r"(a[9]), "=r"(a[10]), "=r"(a[11]), "=r"(a[12]), "=r"(a[13]), "=r"(a[14]), "=r"(a[15])
+      : "r"(addr_re));
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];\n"
+      : "=r"(b[0]), "=r"(b[1]), "=r"(b[2]), "=r"(b[3]), "=r"(b[4]), "=r"(b[5]), "=r"(b[6]), "=r"(b[7]), "=r"(b[8]),
+        "=r"(b[9]), "=r"(b[10]), "=r"(b[11]), "=r"(b[12]), "=r"(b[13]), "=r"(b[14]), "=r"(b[15])
+      : "r"(addr_im));
+  asm volatile("tcgen05.wait::ld.sync.aligned;\n"
+               : "+r"(a[0]), "+r"(a[1]), "+r"(a[2]), "+r"(a[3]), "+r"(a[4]), "+r"(a[5]), "+r"(a[6]), "+r"(a[7]),
+                 "+r"(a[8]), "+r"(a[9]), "+r"(a[10]), "+r"(a[11]), "+r"(a[12]), "+r"(a[13]), "+r"(a[14]), "+r"(a[15]),
+                 "+r"(b[0]), "+r"(b[1]), "+r"(b[2]), "+r"(b[3]), "+r"(b[4]), "+r"(b[5]), "+r"(b[6]), "+r"(b[7]),
+                 "+r"(b[8]), "+r"(b[9]), "+r"(b[10]), "+r"(b[11]), "+r"(b[12]), "+r"(b[13]), "+r"(b[14]), "+r"(b[15])
+               :
+               : "memory");
+#pragma unroll
+  for (int i = 0; i < 16; ++i) { re[i] = __uint_as_float(a[i]); im[i] = __uint_as_float(b[i]); }
+}
+// 8 TMEM columns of this thread's lane for Re and for Im.
+__device__ __forceinline__ void c_tmem_ld8x2(uint32_t addr_re, uint32_t addr_im, float (&re)[8], float (&im)[8]) {
+  uint32_t a[8], b[8];
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];\n"
+               : "=r"(a[0]), "=r"(a[1]), "=r"(a[2]), "=r"(a[3]), "=r"(a[4]), "=r"(a[5]), "=r"(a[6]), "=r"(a[7])
+               : "r"(addr_re));
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];\n"
+               : "=r"(b[0]), "=r"(b[1]), "=r"(b[2]), "=r"(b[3]), "=r"(b[4]), "=r"(b[5]), "=r"(b[6]), "=r"(b[7])
+               : "r"(addr_im));
+  asm volatile("tcgen05.wait::ld.sync.aligned;\n"
+               : "+r"(a[0]), "+r"(a[1]), "+r"(a[2]), "+r"(a[3]), "+r"(a[4]), "+r"(a[5]), "+r"(a[6]), "+r"(a[7]),
+                 "+r"(b[0]), "+r"(b[1]), "+r"(b[2]), "+r"(b[3]), "+r"(b[4]), "+r"(b[5]), "+r"(b[6]), "+r"(b[7])
+               :
+               : "memory");
+#pragma unroll
+  for (int i = 0; i < 8; ++i) { re[i] = __uint_as_float(a[i]); im[i] = __uint_as_float(b[i]); }
+}
+// x = hi + lo with hi the 11-bit truncation of x (exact in fp16 for the pre-scaled range).
+__device__ __forceinline__ void c_split2(float x0, float x1, uint32_t& hi, uint32_t& lo) {
+  const float h0 = __uint_as_float(__float_as_uint(x0) & 0xFFFFE000u);
+  const float h1 = __uint_as_float(__float_as_uint(x1) & 0xFFFFE000u);
+  asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(hi) : "f"(h1), "f"(h0));
+  asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(lo) : "f"(x1 - h1), "f"(x0 - h0));
+}
+
+// ------------------------------------------------------------------------------ the kernel
+struct ChainShared {
+  unsigned long long mma_bar;
+  unsigned long long load_bar;
+  uint32_t tmem_base;
+  float red_max[kCThreads / 32], red_sum[kCThreads / 32], red_cnt[kCThreads / 32], red_v[kCThreads / 32];
+  float xch[2][2][4];            // [parity][cluster rank][R_true, owned sum, owned NaN count, -]
+  float px[kCMaxExtra * 128];    // power spectrum of the extra frames [frame][bin slot]
+  int mel_k0[kMaxMels];
+  float mel_w0[kMaxMels], mel_w1[kMaxMels];
+};
+
+__device__ __forceinline__ float block_max_nan(float v, float* red, int lane, int warp) {
+  v = warp_max_nan(v);
+  if (lane == 0) red[warp] = v;
+  __syncthreads();
+  float r = red[0];
+#pragma unroll
+  for (int w = 1; w < kCThreads / 32; ++w) r = max_nan(r, red[w]);
+  return r;
+}
+__device__ __forceinline__ float block_sum(float v, float* red, int lane, int warp) {
+  v = warp_sum(v);
+  if (lane == 0) red[warp] = v;
+  __syncthreads();
+  float r = 0.f;
+#pragma unroll
+  for (int w = 0; w < kCThreads / 32; ++w) r += red[w];
+  return r;
+}
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kCThreads, 1)
+melspec_chain_kernel(const ChainArgs a) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  unsigned char* tab = smem_raw;                                       // Ch | Cl | Sh | Sl
+  unsigned char* tiles = tab + 4 * kCTabBytes;                         // Eh | El | Oh | Ol
+  float* ybuf = reinterpret_cast<float*>(tiles + 4 * kCTileBytes);     // 2 x kCYFloats
+  float* stage = ybuf + 2 * kCYFloats;                                 // 2 x kCStageFloats
+  unsigned char* xt = reinterpret_cast<unsigned char*>(stage + 2 * kCStageFloats);   // Exh | Exl | Oxh | Oxl
+  __shared__ ChainShared sh;
+
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int h = (int)c_cluster_rank(), peer = h ^ 1;
+  const long long cluster_id = blockIdx.x >> 1, n_clusters = gridDim.x >> 1;
+  const long long n_my_items =
+      a.n_items > cluster_id ? (a.n_items - cluster_id + n_clusters - 1) / n_clusters : 0;
+  const int J = (int)(n_my_items * a.ppc);
+  if (J == 0) return;   // both CTAs of the cluster agree
+
+  const uint32_t mma_bar = c_smem_u32(&sh.mma_bar), load_bar = c_smem_u32(&sh.load_bar);
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(c_smem_u32(&sh.tmem_base)), "r"(512));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
+  }
+  if (tid == 32) {
+    c_mbar_init(mma_bar, 4);
+    c_mbar_init(load_bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::);
+  }
+  {
+    const uint4* src = reinterpret_cast<const uint4*>(a.tab);
+    uint4* dst = reinterpret_cast<uint4*>(tab);
+    for (int i = tid; i < 4 * kCTabBytes / 16; i += kCThreads) dst[i] = __ldg(src + i);
+    float4* yz = reinterpret_cast<float4*>(ybuf);
+    for (int i = tid; i < 2 * kCYFloats / 4; i += kCThreads) yz[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    uint4* xz = reinterpret_cast<uint4*>(xt);
+    for (int i = tid; i < 4 * kCXTileBytes / 16; i += kCThreads) xz[i] = make_uint4(0u, 0u, 0u, 0u);
+    for (int i = tid; i < a.n_mels; i += kCThreads) {
+      sh.mel_k0[i] = a.mel_k0[i];
+      sh.mel_w0[i] = a.mel_w0[i];
+      sh.mel_w1[i] = a.mel_w1[i];
+    }
+  }
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  asm volatile("tcgen05.fence::before_thread_sync;" ::);
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::);
+  const uint32_t tmem_base = sh.tmem_base;
+
+  const int seg_lo = a.seg_lo[h], seg_n = a.seg_n[h];
+  const int own_lo = max(0, (h ? a.crop / 2 : 0) - seg_lo) >> 2;             // float4 units
+  const int own_hi = min(seg_n, (h ? a.crop : a.crop / 2) - seg_lo) >> 2;
+  const int t_frame = tid & (kTileFrames - 1), grp = tid >> 7;               // grp == mel half
+  const int n_extra = h ? min(a.n_frames - a.n_time, kCMaxExtra) : 0;
+
+  auto pair_of = [&](int j, long long& rec, int& chain) {
+    const long long item = cluster_id + (long long)(j / a.ppc) * n_clusters;
+    rec = item / a.n_chains;
+    chain = (int)(item - rec * a.n_chains);
+    return chain * a.ppc + j % a.ppc;
+  };
+  auto issue_load = [&](int j) {   // one thread: both electrode rows of pair j -> staging
+    long long rec;
+    int chain;
+    const int pr = pair_of(j, rec, chain);
+    const float* base = a.eeg + rec * a.rec_stride + a.crop_off + seg_lo;
+    const uint32_t bytes = (uint32_t)seg_n * 4u;
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    c_mbar_expect_tx(load_bar, 2 * bytes);
+    c_bulk_g2s(c_smem_u32(stage), base + a.pair_a[pr] * a.ch_stride, bytes, load_bar);
+    c_bulk_g2s(c_smem_u32(stage + kCStageFloats), base + a.pair_b[pr] * a.ch_stride, bytes, load_bar);
+  };
+
+  // Difference + statistics of pair j into ybuf[j & 1].  Returns block-uniform values.
+  float st_amax = 0.f, st_sum = 0.f, st_cnt = 0.f;
+  auto diff_pass = [&](int j) {
+    c_mbar_wait(load_bar, j & 1);
+    const float4* sa = reinterpret_cast<const float4*>(stage);
+    const float4* sb = reinterpret_cast<const float4*>(stage + kCStageFloats);
+    float4* yd = reinterpret_cast<float4*>(ybuf + (j & 1) * kCYFloats + kCMargin);
+    float amax = 0.f, sum = 0.f;
+    for (int i = tid; i < (seg_n >> 2); i += kCThreads) {
+      const float4 x = sa[i], y = sb[i];
+      const float4 d = make_float4(x.x - y.x, x.y - y.y, x.z - y.z, x.w - y.w);
+      yd[i] = d;
+      amax = max_nan(max_nan(amax, fabsf(d.x)), max_nan(fabsf(d.y), max_nan(fabsf(d.z), fabsf(d.w))));
+      const float s4 = (d.x + d.y) + (d.z + d.w);
+      sum += (i >= own_lo && i < own_hi) ? s4 : 0.f;
+    }
+    st_amax = block_max_nan(amax, sh.red_max, lane, warp);
+    st_sum = block_sum(sum, sh.red_sum, lane, warp);
+    st_cnt = 0.f;
+    if (st_amax != st_amax) {   // NaN samples present (rare): count them, sum and max the rest
+      const float* ys = ybuf + (j & 1) * kCYFloats + kCMargin;
+      float m = 0.f, s = 0.f, c = 0.f;
+      for (int i = tid; i < seg_n; i += kCThreads) {
+        const float d = ys[i];
+        const bool own = (i >> 2) >= own_lo && (i >> 2) < own_hi;
+        if (d != d) { if (own) c += 1.f; } else { m = fmaxf(m, fabsf(d)); if (own) s += d; }
+      }
+      __syncthreads();
+      st_amax = block_max_nan(m, sh.red_max, lane, warp);
+      st_sum = block_sum(s, sh.red_sum, lane, warp);
+      st_cnt = block_sum(c, sh.red_cnt, lane, warp);
+    }
+  };
+  auto publish = [&](int parity, float r_true) {   // my {R, sum, count} -> both CTAs of the cluster
+    if (tid == 0) {
+      float* mine = sh.xch[parity][h];
+      mine[0] = r_true; mine[1] = st_sum; mine[2] = st_cnt;
+      const uint32_t la = c_smem_u32(mine);
+      c_st_peer_f32(la, peer, r_true);
+      c_st_peer_f32(la + 4, peer, st_sum);
+      c_st_peer_f32(la + 8, peer, st_cnt);
+    }
+    if (warp == 0) c_cluster_arrive(); else c_cluster_arrive_relaxed();   // only warp 0 wrote
+  };
+
+  float acc[64], qprev[64];
+#pragma unroll
+  for (int i = 0; i < 64; ++i) { acc[i] = 0.f; qprev[i] = 0.f; }
+  float csum = 0.f;
+  int e_jm1 = 0, e_jm2 = 0;
+
+  auto flush = [&](int j_last, float t_fold) {   // write the item whose last tile is j_last
+    long long rec;
+    int chain;
+    pair_of(j_last, rec, chain);
+    float* o = a.out + ((rec * a.n_mels + 64 * grp) * (long long)a.n_time + 128 * h + t_frame) * a.n_chains + chain;
+    const long long mstride = (long long)a.n_time * a.n_chains;
+#pragma unroll
+    for (int i = 0; i < 64; ++i)
+      o[i * mstride] = fmaf(a.out_gain, acc[i] + fmaxf(qprev[i], t_fold) - csum, a.out_bias);
+  };
+
+  // ---- prologue: first pair
+  if (tid == 0) issue_load(0);
+  diff_pass(0);
+  __syncthreads();
+  if (tid == 0 && J > 1) issue_load(1);
+  publish(1, 0.f);
+
+  // ---- main loop: iteration j builds + issues tile j, then runs the epilogue of tile j-1
+  for (int j = 0; j <= J; ++j) {
+    c_cluster_wait();
+    const float(*xc)[4] = sh.xch[(j + 1) & 1];
+    float t_prev = 0.f;   // clip threshold of tile j-2 in that tile's scaled log2 units
+    if (j >= 2) {
+      const float r_pair = fmaxf(fmaxf(xc[0][0], xc[1][0]), a.log2_amin);
+      const float off = 2.f * (float)e_jm2;
+      t_prev = fmaxf(a.log2_amin, r_pair - a.top_log2) + off;
+      csum += r_pair + off;
+    }
+    int e_j = 0;
+    if (j < J) {
+      float* yb = ybuf + (j & 1) * kCYFloats;
+      float amax = st_amax;
+      const float n_nan = xc[0][2] + xc[1][2];
+      if (n_nan > 0.f) {   // cfg_utils.py:380-385 on the difference: nanmean fill, all-NaN -> 0
+        const bool all_nan = n_nan >= (float)a.crop;
+        const float fill = all_nan ? 0.f : (xc[0][1] + xc[1][1]) / ((float)a.crop - n_nan);
+        float m = 0.f;
+        for (int i = tid; i < seg_n; i += kCThreads) {
+          float d = yb[kCMargin + i];
+          if (all_nan) d = 0.f; else if (d != d) d = fill;
+          yb[kCMargin + i] = d;
+          m = fmaxf(m, fabsf(d));
+        }
+        amax = block_max_nan(m, sh.red_max, lane, warp);
+      }
+      if (a.pad_mode == 1) {   // reflect padding (librosa < 0.10); zero padding is the resident state
+        __syncthreads();
+        for (int k = tid; k < 2 * kCMargin + 128; k += kCThreads) {
+          const int idx = k < kCMargin ? k : seg_n + k;          // left margin | right margin
+          const int i = seg_lo + idx - kCMargin;                 // crop coordinate
+          const int src = i < 0 ? -i : (i >= a.crop ? 2 * (a.crop - 1) - i : -1);
+          const int sidx = src - seg_lo;
+          if (idx < kCYFloats) yb[idx] = (src >= 0 && sidx >= 0 && sidx < seg_n) ? yb[kCMargin + sidx] : 0.f;
+        }
+        __syncthreads();
+      }
+      // exact power-of-two pre-scale: amax * 2^e in [2^10, 2^11)
+      {
+        int ex = 0;
+        if (amax > 0.f && amax < __int_as_float(0x7f800000)) { frexpf(amax, &ex); e_j = 11 - ex; }
+        e_j = max(-60, min(60, e_j));
+      }
+      const float s = __int_as_float((127 + e_j) << 23);
+
+      if (j >= 1) c_mbar_wait(mma_bar, (j - 1) & 1);   // tile j-1 no longer reads the operand tiles
+      asm volatile("tcgen05.fence::after_thread_sync;" ::);
+
+      // operand build: thread = (frame, 32 fold indices); E = s(y[c+m] + y[c-m]), O = s(y[c+m] - y[c-m])
+      {
+        const float* yc = yb + kCMargin + (128 * h + t_frame) * a.hop - seg_lo;
+#pragma unroll 1
+        for (int o = 0; o < 4; ++o) {
+          const int m0 = 32 * grp + 8 * o;
+          float ev[8], ov[8];
+#pragma unroll
+          for (int q = 0; q < 8; ++q) {
+            const float yp = yc[m0 + q], yms = yc[-(m0 + q)] * s;
+            ev[q] = fmaf(yp, s, yms);
+            ov[q] = fmaf(yp, s, -yms);
+          }
+          uint4 eh, el, oh, ol;
+          c_split2(ev[0], ev[1], eh.x, el.x); c_split2(ev[2], ev[3], eh.y, el.y);
+          c_split2(ev[4], ev[5], eh.z, el.z); c_split2(ev[6], ev[7], eh.w, el.w);
+          c_split2(ov[0], ov[1], oh.x, ol.x); c_split2(ov[2], ov[3], oh.y, ol.y);
+          c_split2(ov[4], ov[5], oh.z, ol.z); c_split2(ov[6], ov[7], oh.w, ol.w);
+          const int off = c_umma_offset(t_frame, m0);
+          *reinterpret_cast<uint4*>(tiles + 0 * kCTileBytes + off) = eh;
+          *reinterpret_cast<uint4*>(tiles + 1 * kCTileBytes + off) = el;
+          *reinterpret_cast<uint4*>(tiles + 2 * kCTileBytes + off) = oh;
+          *reinterpret_cast<uint4*>(tiles + 3 * kCTileBytes + off) = ol;
+        }
+      }
+      // frames beyond the kept width (they only feed the pair maximum) become rows of a small
+      // second B operand: one (frame, fold index) element per thread
+      if (tid < n_extra * kFold) {
+        const int x = tid >> 6, m = tid & (kFold - 1);
+        const float* yc = yb + kCMargin + (a.n_time + x) * a.hop - seg_lo;
+        const float yp = yc[m], yms = yc[-m] * s;
+        const float e = fmaf(yp, s, yms), o = fmaf(yp, s, -yms);
+        const float eh = __uint_as_float(__float_as_uint(e) & 0xFFFFE000u);
+        const float oh = __uint_as_float(__float_as_uint(o) & 0xFFFFE000u);
+        const int off = c_umma_offset(x, m);
+        *reinterpret_cast<__half*>(xt + 0 * kCXTileBytes + off) = __float2half_rn(eh);
+        *reinterpret_cast<__half*>(xt + 1 * kCXTileBytes + off) = __float2half_rn(e - eh);
+        *reinterpret_cast<__half*>(xt + 2 * kCXTileBytes + off) = __float2half_rn(oh);
+        *reinterpret_cast<__half*>(xt + 3 * kCXTileBytes + off) = __float2half_rn(o - oh);
+      }
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      asm volatile("tcgen05.fence::before_thread_sync;" ::);
+      __syncthreads();
+      // MMA issue, spread over four warps (one per scheduler): Re, Im, extra Re, extra Im are
+      // independent accumulators; each issuing thread commits to the same mbarrier (count 4).
+      if (warp < 4 && lane == 0) {
+        asm volatile("tcgen05.fence::after_thread_sync;" ::);
+        uint32_t tab0 = c_smem_u32(tab), til0 = c_smem_u32(tiles), xt0 = c_smem_u32(xt);
+        // opaque to the optimiser: keeps the descriptors out of the loop-invariant (spilled) set
+        asm volatile("" : "+r"(tab0), "+r"(til0), "+r"(xt0));
+        const int part = warp & 1;
+        if (warp < 2 || n_extra > 0) {
+          const bool big = warp < 2;
+          // big: D[frame][bin] = tiles (A) x tables (B); extra: D'[bin][frame] = tables (A) x xt (B)
+          const uint32_t d = big ? tmem_base + (j & 1) * kCAccCols + part * kCBins
+                                 : tmem_base + kCXTmemCol + (j & 1) * 2 * kCXCols + part * kCXCols;
+          const uint32_t t_hi = tab0 + (2 * part) * kCTabBytes, t_lo = t_hi + kCTabBytes;
+          const uint32_t f_hi = big ? til0 + (2 * part) * kCTileBytes : xt0 + (2 * part) * kCXTileBytes;
+          const uint32_t f_lo = f_hi + (big ? kCTileBytes : kCXTileBytes);
+          const uint32_t idesc = big ? kCIdesc : kCIdescX;
+          uint32_t accum = 0;
+#pragma unroll 1
+          for (int term = 0; term < 3; ++term) {   // hi.hi + lo.hi + hi.lo  (frames x tables)
+            const uint32_t ff = term == 1 ? f_lo : f_hi, tt = term == 2 ? t_lo : t_hi;
+            const uint64_t fd = c_umma_desc(ff), td = c_umma_desc(tt);
+#pragma unroll
+            for (int ks = 0; ks < kFold / 16; ++ks) {
+              const uint64_t fdk = fd + (uint64_t)(ks * 16), tdk = td + (uint64_t)(ks * 16);
+              c_umma(d, big ? fdk : tdk, big ? tdk : fdk, accum, idesc);
+              accum = 1;
+            }
+          }
+        }
+        asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(mma_bar) : "memory");
+      }
+    }
+
+    float r_true = 0.f;
+    if (j >= 1) {
+      const int jt = j - 1;
+      if (j == J) c_mbar_wait(mma_bar, jt & 1);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::);
+      float t_fold = t_prev;
+      if (jt % a.ppc == 0) {   // first pair of an item: write the finished one, start afresh
+        if (jt > 0) flush(jt - 1, t_prev);
+#pragma unroll
+        for (int i = 0; i < 64; ++i) { acc[i] = 0.f; qprev[i] = 0.f; }
+        csum = 0.f;
+        t_fold = 0.f;
+      }
+      const uint32_t lane_addr = tmem_base + ((uint32_t)(32 * (warp & 3)) << 16) + (jt & 1) * kCAccCols;
+      float vmax = 0.f;
+      float re[8], im[8];
+#define CH_POW(s, i) const float p##s = fmaf(re[i], re[i], im[i] * im[i]);
+#define CH_MEL_TAIL(i)                       \
+  vmax = fmaxf(vmax, v);                     \
+  acc[i] += fmaxf(qprev[i], t_fold);         \
+  qprev[i] = c_lg2(v);
+#define CH_MEL1(i, sa, w0) { const float v = (w0) * p##sa; CH_MEL_TAIL(i) }
+#define CH_MEL2(i, sa, sb, w0, w1) { const float v = fmaf(w1, p##sb, (w0) * p##sa); CH_MEL_TAIL(i) }
+      if (grp == 0) {
+#define CH_LOAD(c) c_tmem_ld8x2(lane_addr + MELGEN_COL0_H0 + 8 * (c), lane_addr + kCBins + MELGEN_COL0_H0 + 8 * (c), re, im);
+        MELGEN_EPILOGUE_H0(CH_LOAD, CH_POW, CH_MEL1, CH_MEL2)
+#undef CH_LOAD
+      } else {
+#define CH_LOAD(c) c_tmem_ld8x2(lane_addr + MELGEN_COL0_H1 + 8 * (c), lane_addr + kCBins + MELGEN_COL0_H1 + 8 * (c), re, im);
+        MELGEN_EPILOGUE_H1(CH_LOAD, CH_POW, CH_MEL1, CH_MEL2)
+#undef CH_LOAD
+      }
+#undef CH_POW
+#undef CH_MEL_TAIL
+#undef CH_MEL1
+#undef CH_MEL2
+      asm volatile("tcgen05.fence::before_thread_sync;" ::);
+
+      // extra frames: lane = bin slot, column = frame; power -> shared -> mel maximum
+      if (n_extra > 0) {
+        if (warp < 4) {
+          const uint32_t xaddr = tmem_base + ((uint32_t)(32 * warp) << 16) + kCXTmemCol + (jt & 1) * 2 * kCXCols;
+          float xr[4], xi[4];
+          c_tmem_ld4(xaddr, xr);
+          c_tmem_ld4(xaddr + kCXCols, xi);
+#pragma unroll
+          for (int x = 0; x < kCMaxExtra; ++x) sh.px[x * 128 + tid] = fmaf(xr[x], xr[x], xi[x] * xi[x]);
+        }
+        asm volatile("tcgen05.fence::before_thread_sync;" ::);
+        __syncthreads();
+        for (int i = tid; i < n_extra * a.n_mels; i += kCThreads) {
+          const int x = i / a.n_mels, m = i % a.n_mels;
+          const int k0 = sh.mel_k0[m];
+          vmax = fmaxf(vmax, fmaf(sh.mel_w1[m], sh.px[x * 128 + k0 + 1], sh.mel_w0[m] * sh.px[x * 128 + k0]));
+        }
+      }
+      const float vm = block_max_nan(vmax, sh.red_v, lane, warp);
+      r_true = c_lg2(vm) - 2.f * (float)e_jm1;
+    }
+
+    if (j + 1 < J) {
+      diff_pass(j + 1);   // ends with a block barrier: staging is free again
+      if (tid == 0 && j + 2 < J) issue_load(j + 2);
+    }
+    publish(j & 1, r_true);
+    e_jm2 = e_jm1;
+    e_jm1 = e_j;
+  }
+
+  // ---- drain: the last pair's maximum has been exchanged; write the last item
+  c_cluster_wait();
+  {
+    const float(*xc)[4] = sh.xch[J & 1];
+    const float r_pair = fmaxf(fmaxf(xc[0][0], xc[1][0]), a.log2_amin);
+    const float off = 2.f * (float)e_jm2;
+    csum += r_pair + off;
+    flush(J - 1, fmaxf(a.log2_amin, r_pair - a.top_log2) + off);
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::);
+  __syncthreads();
+  if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512));
+  // the peer may still be writing into this CTA's shared memory until it has passed the last wait
+  c_cluster_arrive();
+  c_cluster_wait();
+}
+
+// ------------------------------------------------------------------------------------- host
+size_t melspec_chain_smem_bytes() {
+  return 4 * (size_t)kCTabBytes + 4 * (size_t)kCTileBytes + sizeof(float) * (2 * (size_t)kCYFloats + 2 * (size_t)kCStageFloats) +
+         4 * (size_t)kCXTileBytes;
+}
+
+// The generated epilogue is only valid for the bank it was generated from.
+bool melspec_chain_bank_matches(const eegspec_mel_params& p, int k_lo, const int* k0, const float* w0,
+                                const float* w1) {
+  if (p.sr != MELGEN_SR || p.n_fft != MELGEN_NFFT || p.n_mels != MELGEN_NMELS || k_lo != MELGEN_KLO) return false;
+  for (int m = 0; m < MELGEN_NMELS; ++m) {
+    if (k0[m] != kGenK0[m]) return false;
+    if (fabsf(w0[m] - kGenW0[m]) > 2e-6f * fabsf(kGenW0[m])) return false;
+    if (fabsf(w1[m] - kGenW1[m]) > 2e-6f * fabsf(kGenW1[m]) + 1e-12f) return false;
+  }
+  return true;
+}
+
+// Returns EEGSPEC_EUNSUPPORTED when this geometry / layout is not served by engine 3.
+int melspec_chain_launch(const MelArgs& m, const eegspec_mel_params& p, long long batch, cudaStream_t st) {
+  if (p.time_major || m.n_time != 2 * kTileFrames || m.n_frames < m.n_time) return EEGSPEC_EUNSUPPORTED;
+  if (m.n_frames - m.n_time > kCMaxExtra || m.hop > 40 || m.hop < 1 || (m.crop & 7)) return EEGSPEC_EUNSUPPORTED;
+  if ((reinterpret_cast<uintptr_t>(m.eeg) & 15) || (m.rec_stride & 3) || (m.ch_stride & 3) || (m.crop_off & 3))
+    return EEGSPEC_EUNSUPPORTED;
+  ChainArgs a;
+  a.eeg = m.eeg;
+  a.out = m.out;
+  a.tab = m.t.tc3_tab;
+  a.mel_k0 = m.t.mel_k0;
+  a.mel_w0 = m.t.mel_w0;
+  a.mel_w1 = m.t.mel_w1;
+  a.rec_stride = m.rec_stride;
+  a.ch_stride = m.ch_stride;
+  a.n_items = batch * m.n_chains;
+  a.crop = m.crop;
+  a.crop_off = m.crop_off;
+  a.hop = m.hop;
+  a.n_frames = m.n_frames;
+  a.n_mels = m.n_mels;
+  a.n_time = m.n_time;
+  a.n_chains = m.n_chains;
+  a.ppc = m.ppc;
+  a.pad_mode = m.pad_mode;
+  const int last = (m.n_frames < m.n_time + kCMaxExtra ? m.n_frames : m.n_time + kCMaxExtra) - 1;
+  auto up4 = [](int v) { return (v + 3) & ~3; };
+  a.seg_lo[0] = 0;
+  a.seg_n[0] = (up4((kTileFrames - 1) * m.hop + 64) < m.crop ? up4((kTileFrames - 1) * m.hop + 64) : m.crop);
+  a.seg_lo[1] = (kTileFrames * m.hop - 63) & ~3;
+  const int hi1 = up4(last * m.hop + 64) < m.crop ? up4(last * m.hop + 64) : m.crop;
+  a.seg_n[1] = hi1 - a.seg_lo[1];
+  for (int h = 0; h < 2; ++h)
+    if (a.seg_n[h] <= 0 || a.seg_n[h] > kCStageFloats || a.seg_lo[h] < 0) return EEGSPEC_EUNSUPPORTED;
+  if (a.seg_lo[1] + a.seg_n[1] < m.crop && last * m.hop + 64 > a.seg_lo[1] + a.seg_n[1]) return EEGSPEC_EUNSUPPORTED;
+  a.log2_amin = log2f(m.amin);
+  a.top_log2 = m.top_db / kLog2To10Log10;
+  a.out_bias = m.db_offset * m.inv_db_scale;
+  a.out_gain = kLog2To10Log10 * m.inv_db_scale / (float)m.ppc;
+  for (int i = 0; i < EEGSPEC_MAX_PAIRS; ++i) { a.pair_a[i] = m.pair_a[i]; a.pair_b[i] = m.pair_b[i]; }
+
+  static bool configured[64] = {};
+  static int sm_count[64] = {};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 0 || dev >= 64) return EEGSPEC_EUNSUPPORTED;
+  const size_t smem = melspec_chain_smem_bytes();
+  if (!configured[dev]) {
+    cudaError_t e = cudaFuncSetAttribute(melspec_chain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return (int)e;
+    e = cudaDeviceGetAttribute(&sm_count[dev], cudaDevAttrMultiProcessorCount, dev);
+    if (e != cudaSuccess) return (int)e;
+    configured[dev] = true;
+  }
+  long long clusters = sm_count[dev] / 2;
+  if (clusters < 1) clusters = 1;
+  if (clusters > a.n_items) clusters = a.n_items;
+  if ((a.n_items + clusters - 1) / clusters * a.ppc > (1LL << 30)) return EEGSPEC_EUNSUPPORTED;
+  melspec_chain_kernel<<<(unsigned)(2 * clusters), kCThreads, smem, st>>>(a);
+  count_launch();
+  return (int)cudaGetLastError();
+}
+
+}  // namespace eegspec

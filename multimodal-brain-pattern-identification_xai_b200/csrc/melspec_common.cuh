@@ -23,6 +23,7 @@ struct MelTables {            // device-resident constant tables for one paramet
   float* mel_w0;              // [n_mels]
   float* mel_w1;              // [n_mels]
   unsigned short* tc_tab;     // engine 2: fp16 {cos hi, cos lo, sin hi, sin lo} in UMMA layout
+  unsigned short* tc3_tab;    // engine 3: the same with the Hann window folded in (row 0 halved)
 };
 
 struct MelArgs {
@@ -54,5 +55,10 @@ size_t melspec_tc_smem_bytes(int crop);
 int melspec_tc_launch_pair(const MelArgs& a, int n_pairs, long long n_records, cudaStream_t st);
 constexpr int kTcTableHalves = 4 * 112 * kFold;
 void melspec_tc_build_tables(const double* cos_d, const double* sin_d, int n_bins, unsigned short* out);
+
+// Engine 3 (melspec_chain.cu): persistent clustered kernel, no scratch.
+bool melspec_chain_bank_matches(const eegspec_mel_params& p, int k_lo, const int* k0, const float* w0,
+                                const float* w1);
+int melspec_chain_launch(const MelArgs& m, const eegspec_mel_params& p, long long batch, cudaStream_t st);
 
 }  // namespace eegspec

@@ -22,7 +22,7 @@ def run(x, **kw):
     return y.cpu().numpy()
 
 
-ENGINES = [pytest.param(2, id="tcgen05"), pytest.param(1, id="simt")]   # 0 (default) == 2
+ENGINES = [pytest.param(3, id="chain"), pytest.param(2, id="tcgen05"), pytest.param(1, id="simt")]   # 0 (default) == 3 here
 
 
 @pytest.mark.parametrize("engine", ENGINES)
@@ -54,7 +54,7 @@ def test_tensor_core_engine_is_scale_invariant(scale):
     rng = np.random.default_rng(26)
     x = eeg_like(rng, (1, 20, 10000)) * np.float32(scale)
     want = mo.eeg_to_spectrogram_batch_oracle(x)
-    for engine in (2, 1):
+    for engine in (3, 2, 1):
         err = np.abs(run(x, engine=engine) - want).max()
         assert err <= ATOL, f"engine {engine} scale {scale}: max abs err {err:.3e}"
 
@@ -62,8 +62,8 @@ def test_tensor_core_engine_is_scale_invariant(scale):
 def test_engines_agree_at_size():
     rng = np.random.default_rng(27)
     x = eeg_like(rng, (40, 20, 10000))
-    a, b = run(x, engine=2), run(x, engine=1)
-    assert np.abs(a - b).max() <= 2e-4
+    a, b, c = run(x, engine=2), run(x, engine=1), run(x, engine=3)
+    assert np.abs(a - b).max() <= 2e-4 and np.abs(c - b).max() <= 2e-4
 
 
 def test_single_record_time_major_and_crop():
@@ -74,7 +74,7 @@ def test_single_record_time_major_and_crop():
     assert got.shape == (128, 256, 4)
     assert np.abs(got - want).max() <= ATOL
     tm = b200spec.spectrogram_from_eeg(torch.from_numpy(np.ascontiguousarray(x.T)).cuda())
-    assert np.abs(tm.cpu().numpy() - got).max() <= 1e-6
+    assert np.abs(tm.cpu().numpy() - got).max() <= 1e-4      # time-major input runs on engine 2
     mid = run(x[:, 4000:14000])
     assert np.abs(mid - got).max() == 0.0                    # crop offset is exact integer math
 

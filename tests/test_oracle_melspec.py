@@ -71,3 +71,18 @@ def test_image_properties(melspec_golden):
     x = melspec_golden["range/x"][0]
     db = mo.pair_melspec_db(mo.fill_missing(x[0] - x[4]))
     assert (db == -80.0).mean() > 0.05 and db.max() == 0.0
+
+
+def test_generated_mel_epilogue_is_current_and_matches_the_bank():
+    """csrc/mel_default_epilogue.h (literal taps of engine 3) must be what the generator emits
+    for the oracle's Slaney bank."""
+    import importlib.util
+    import os
+
+    from conftest import ROOT
+
+    spec = importlib.util.spec_from_file_location("gen_mel", os.path.join(ROOT, "tools", "gen_mel_epilogue.py"))
+    gen = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(gen)
+    with open(gen.OUT) as fh:
+        assert fh.read() == gen.render()
