@@ -18,13 +18,13 @@
 // differencing /root/reference/root/src/utils/data_utils.py:183-215, crop
 // /root/reference/root/src/utils/cfg_utils.py:369-371, NaN fill cfg_utils.py:380-385).
 #include <cuda_fp16.h>
+#include <stdlib.h>
 
 #include "mel_default_epilogue.h"
 #include "melspec_common.cuh"
 
 namespace eegspec {
 
-constexpr int kCThreads = 256;
 constexpr int kCBins = 112;                         // MMA N
 constexpr int kCTabBytes = kCBins * kFold * 2;      // 14 336
 constexpr int kCTileBytes = kTileFrames * kFold * 2;  // 16 384
@@ -185,39 +185,55 @@ __device__ __forceinline__ void c_split2(float x0, float x1, uint32_t& hi, uint3
   asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(lo) : "f"(x1 - h1), "f"(x0 - h0));
 }
 
+// ------------------------------------------------------------------------------ more helpers
+__device__ __forceinline__ void c_mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+// wait with cluster-scope acquire: the data was written by the peer CTA (st.shared::cluster)
+__device__ __forceinline__ void c_mbar_wait_cluster(uint32_t bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t.reg .pred P1;\n\t"
+      "CX_%=:\n\t"
+      "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 P1, [%0], %1;\n\t"
+      "@!P1 bra CX_%=;\n\t}\n"
+      :
+      : "r"(bar), "r"(parity)
+      : "memory");
+}
+// arrive on the mbarrier at the same shared-memory offset in CTA `rank` of the cluster
+__device__ __forceinline__ void c_mbar_arrive_cluster(uint32_t local_bar, uint32_t rank) {
+  uint32_t remote;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local_bar), "r"(rank));
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(remote) : "memory");
+}
+__device__ __forceinline__ void c_named_bar(int id, int threads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
+}
+
 // ------------------------------------------------------------------------------ the kernel
+// Thread roles (NQ = mel parts per frame):  warps 0 .. 4 NQ - 1 compute -- thread = (frame t,
+// part q): builds 64/NQ fold indices of frame t's operands and owns mels [q, q+1) * 128/NQ of it;
+// the last warp is the control warp: one lane issues the TMA prefetch, the tcgen05.mma stream
+// and the cross-CTA exchange of the pair maximum.  Compute warps never meet in a CTA-wide
+// barrier except once per tile (y complete); everything else is mbarrier arrive / wait.
+constexpr int kCMaxWarps = 16;
+
 struct ChainShared {
-  unsigned long long mma_bar;
-  unsigned long long load_bar;
+  unsigned long long mma_bar, load_bar, ops_bar, epi_bar, diff_bar, xch_bar[2];
   uint32_t tmem_base;
-  float red_max[kCThreads / 32], red_sum[kCThreads / 32], red_cnt[kCThreads / 32], red_v[kCThreads / 32];
-  float xch[2][2][4];            // [parity][cluster rank][R_true, owned sum, owned NaN count, -]
-  float px[kCMaxExtra * 128];    // power spectrum of the extra frames [frame][bin slot]
+  float w_amax[2][kCMaxWarps];      // per-warp max|y| of pair j (NaN if any NaN), [j & 1]
+  float w_vmax[2][kCMaxWarps];      // per-warp log2 mel maximum of tile j (unscaled units), [j & 1]
+  float xch[2][2];                  // [exchange & 1][cluster rank]: log2 of the pair maximum
+  float red[kCMaxWarps];
+  float px[kCMaxExtra * 128];       // power spectrum of the extra frames [frame][bin slot]
   int mel_k0[kMaxMels];
   float mel_w0[kMaxMels], mel_w1[kMaxMels];
 };
 
-__device__ __forceinline__ float block_max_nan(float v, float* red, int lane, int warp) {
-  v = warp_max_nan(v);
-  if (lane == 0) red[warp] = v;
-  __syncthreads();
-  float r = red[0];
-#pragma unroll
-  for (int w = 1; w < kCThreads / 32; ++w) r = max_nan(r, red[w]);
-  return r;
-}
-__device__ __forceinline__ float block_sum(float v, float* red, int lane, int warp) {
-  v = warp_sum(v);
-  if (lane == 0) red[warp] = v;
-  __syncthreads();
-  float r = 0.f;
-#pragma unroll
-  for (int w = 0; w < kCThreads / 32; ++w) r += red[w];
-  return r;
-}
-
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kCThreads, 1)
+template <int NQ>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(128 * NQ + 128, 1)
 melspec_chain_kernel(const ChainArgs a) {
+  constexpr int kCompute = 128 * NQ, kWarps = 4 * NQ, kMels = 128 / NQ, kOct = 8 / NQ;
   extern __shared__ __align__(128) unsigned char smem_raw[];
   unsigned char* tab = smem_raw;                                       // Ch | Cl | Sh | Sl
   unsigned char* tiles = tab + 4 * kCTabBytes;                         // Eh | El | Oh | Ol
@@ -228,31 +244,38 @@ melspec_chain_kernel(const ChainArgs a) {
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int h = (int)c_cluster_rank(), peer = h ^ 1;
-  const long long cluster_id = blockIdx.x >> 1, n_clusters = gridDim.x >> 1;
-  const long long n_my_items =
-      a.n_items > cluster_id ? (a.n_items - cluster_id + n_clusters - 1) / n_clusters : 0;
-  const int J = (int)(n_my_items * a.ppc);
+  const int cluster_id = blockIdx.x >> 1, n_clusters = gridDim.x >> 1;
+  const int n_items = (int)a.n_items;
+  const int n_my_items = n_items > cluster_id ? (n_items - cluster_id + n_clusters - 1) / n_clusters : 0;
+  const int J = n_my_items * a.ppc;
   if (J == 0) return;   // both CTAs of the cluster agree
 
   const uint32_t mma_bar = c_smem_u32(&sh.mma_bar), load_bar = c_smem_u32(&sh.load_bar);
+  const uint32_t ops_bar = c_smem_u32(&sh.ops_bar), epi_bar = c_smem_u32(&sh.epi_bar);
+  const uint32_t diff_bar = c_smem_u32(&sh.diff_bar);
   if (warp == 0) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(c_smem_u32(&sh.tmem_base)), "r"(512));
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
   }
   if (tid == 32) {
-    c_mbar_init(mma_bar, 4);
+    c_mbar_init(mma_bar, 1);
     c_mbar_init(load_bar, 1);
+    c_mbar_init(ops_bar, kWarps);
+    c_mbar_init(epi_bar, kWarps);
+    c_mbar_init(diff_bar, kWarps);
+    c_mbar_init(c_smem_u32(&sh.xch_bar[0]), 2);
+    c_mbar_init(c_smem_u32(&sh.xch_bar[1]), 2);
     asm volatile("fence.mbarrier_init.release.cluster;" ::);
   }
   {
     const uint4* src = reinterpret_cast<const uint4*>(a.tab);
     uint4* dst = reinterpret_cast<uint4*>(tab);
-    for (int i = tid; i < 4 * kCTabBytes / 16; i += kCThreads) dst[i] = __ldg(src + i);
+    for (int i = tid; i < 4 * kCTabBytes / 16; i += blockDim.x) dst[i] = __ldg(src + i);
     float4* yz = reinterpret_cast<float4*>(ybuf);
-    for (int i = tid; i < 2 * kCYFloats / 4; i += kCThreads) yz[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int i = tid; i < 2 * kCYFloats / 4; i += blockDim.x) yz[i] = make_float4(0.f, 0.f, 0.f, 0.f);
     uint4* xz = reinterpret_cast<uint4*>(xt);
-    for (int i = tid; i < 4 * kCXTileBytes / 16; i += kCThreads) xz[i] = make_uint4(0u, 0u, 0u, 0u);
-    for (int i = tid; i < a.n_mels; i += kCThreads) {
+    for (int i = tid; i < 4 * kCXTileBytes / 16; i += blockDim.x) xz[i] = make_uint4(0u, 0u, 0u, 0u);
+    for (int i = tid; i < a.n_mels; i += blockDim.x) {
       sh.mel_k0[i] = a.mel_k0[i];
       sh.mel_w0[i] = a.mel_w0[i];
       sh.mel_w1[i] = a.mel_w1[i];
@@ -262,244 +285,276 @@ melspec_chain_kernel(const ChainArgs a) {
   asm volatile("tcgen05.fence::before_thread_sync;" ::);
   __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;" ::);
+  c_cluster_arrive();   // the peer's mbarriers are initialised before anyone arrives on them remotely
+  c_cluster_wait();
   const uint32_t tmem_base = sh.tmem_base;
 
   const int seg_lo = a.seg_lo[h], seg_n = a.seg_n[h];
-  const int own_lo = max(0, (h ? a.crop / 2 : 0) - seg_lo) >> 2;             // float4 units
-  const int own_hi = min(seg_n, (h ? a.crop : a.crop / 2) - seg_lo) >> 2;
-  const int t_frame = tid & (kTileFrames - 1), grp = tid >> 7;               // grp == mel half
   const int n_extra = h ? min(a.n_frames - a.n_time, kCMaxExtra) : 0;
 
-  auto pair_of = [&](int j, long long& rec, int& chain) {
-    const long long item = cluster_id + (long long)(j / a.ppc) * n_clusters;
+  auto pair_of = [&](int j, int& rec, int& chain) {
+    const int item = cluster_id + (j / a.ppc) * n_clusters;
     rec = item / a.n_chains;
-    chain = (int)(item - rec * a.n_chains);
+    chain = item - rec * a.n_chains;
     return chain * a.ppc + j % a.ppc;
   };
-  auto issue_load = [&](int j) {   // one thread: both electrode rows of pair j -> staging
-    long long rec;
-    int chain;
-    const int pr = pair_of(j, rec, chain);
-    const float* base = a.eeg + rec * a.rec_stride + a.crop_off + seg_lo;
-    const uint32_t bytes = (uint32_t)seg_n * 4u;
-    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-    c_mbar_expect_tx(load_bar, 2 * bytes);
-    c_bulk_g2s(c_smem_u32(stage), base + a.pair_a[pr] * a.ch_stride, bytes, load_bar);
-    c_bulk_g2s(c_smem_u32(stage + kCStageFloats), base + a.pair_b[pr] * a.ch_stride, bytes, load_bar);
-  };
 
-  // Difference + statistics of pair j into ybuf[j & 1].  Returns block-uniform values.
-  float st_amax = 0.f, st_sum = 0.f, st_cnt = 0.f;
-  auto diff_pass = [&](int j) {
-    c_mbar_wait(load_bar, j & 1);
-    const float4* sa = reinterpret_cast<const float4*>(stage);
-    const float4* sb = reinterpret_cast<const float4*>(stage + kCStageFloats);
-    float4* yd = reinterpret_cast<float4*>(ybuf + (j & 1) * kCYFloats + kCMargin);
-    float amax = 0.f, sum = 0.f;
-    for (int i = tid; i < (seg_n >> 2); i += kCThreads) {
-      const float4 x = sa[i], y = sb[i];
-      const float4 d = make_float4(x.x - y.x, x.y - y.y, x.z - y.z, x.w - y.w);
-      yd[i] = d;
-      amax = max_nan(max_nan(amax, fabsf(d.x)), max_nan(fabsf(d.y), max_nan(fabsf(d.z), fabsf(d.w))));
-      const float s4 = (d.x + d.y) + (d.z + d.w);
-      sum += (i >= own_lo && i < own_hi) ? s4 : 0.f;
-    }
-    st_amax = block_max_nan(amax, sh.red_max, lane, warp);
-    st_sum = block_sum(sum, sh.red_sum, lane, warp);
-    st_cnt = 0.f;
-    if (st_amax != st_amax) {   // NaN samples present (rare): count them, sum and max the rest
-      const float* ys = ybuf + (j & 1) * kCYFloats + kCMargin;
-      float m = 0.f, s = 0.f, c = 0.f;
-      for (int i = tid; i < seg_n; i += kCThreads) {
-        const float d = ys[i];
-        const bool own = (i >> 2) >= own_lo && (i >> 2) < own_hi;
-        if (d != d) { if (own) c += 1.f; } else { m = fmaxf(m, fabsf(d)); if (own) s += d; }
-      }
-      __syncthreads();
-      st_amax = block_max_nan(m, sh.red_max, lane, warp);
-      st_sum = block_sum(s, sh.red_sum, lane, warp);
-      st_cnt = block_sum(c, sh.red_cnt, lane, warp);
-    }
-  };
-  auto publish = [&](int parity, float r_true) {   // my {R, sum, count} -> both CTAs of the cluster
-    if (tid == 0) {
-      float* mine = sh.xch[parity][h];
-      mine[0] = r_true; mine[1] = st_sum; mine[2] = st_cnt;
-      const uint32_t la = c_smem_u32(mine);
-      c_st_peer_f32(la, peer, r_true);
-      c_st_peer_f32(la + 4, peer, st_sum);
-      c_st_peer_f32(la + 8, peer, st_cnt);
-    }
-    if (warp == 0) c_cluster_arrive(); else c_cluster_arrive_relaxed();   // only warp 0 wrote
-  };
-
-  float acc[64], qprev[64];
-#pragma unroll
-  for (int i = 0; i < 64; ++i) { acc[i] = 0.f; qprev[i] = 0.f; }
-  float csum = 0.f;
-  int e_jm1 = 0, e_jm2 = 0;
-
-  auto flush = [&](int j_last, float t_fold) {   // write the item whose last tile is j_last
-    long long rec;
-    int chain;
-    pair_of(j_last, rec, chain);
-    float* o = a.out + ((rec * a.n_mels + 64 * grp) * (long long)a.n_time + 128 * h + t_frame) * a.n_chains + chain;
-    const long long mstride = (long long)a.n_time * a.n_chains;
-#pragma unroll
-    for (int i = 0; i < 64; ++i)
-      o[i * mstride] = fmaf(a.out_gain, acc[i] + fmaxf(qprev[i], t_fold) - csum, a.out_bias);
-  };
-
-  // ---- prologue: first pair
-  if (tid == 0) issue_load(0);
-  diff_pass(0);
-  __syncthreads();
-  if (tid == 0 && J > 1) issue_load(1);
-  publish(1, 0.f);
-
-  // ---- main loop: iteration j builds + issues tile j, then runs the epilogue of tile j-1
-  for (int j = 0; j <= J; ++j) {
-    c_cluster_wait();
-    const float(*xc)[4] = sh.xch[(j + 1) & 1];
-    float t_prev = 0.f;   // clip threshold of tile j-2 in that tile's scaled log2 units
-    if (j >= 2) {
-      const float r_pair = fmaxf(fmaxf(xc[0][0], xc[1][0]), a.log2_amin);
-      const float off = 2.f * (float)e_jm2;
-      t_prev = fmaxf(a.log2_amin, r_pair - a.top_log2) + off;
-      csum += r_pair + off;
-    }
-    int e_j = 0;
-    if (j < J) {
-      float* yb = ybuf + (j & 1) * kCYFloats;
-      float amax = st_amax;
-      const float n_nan = xc[0][2] + xc[1][2];
-      if (n_nan > 0.f) {   // cfg_utils.py:380-385 on the difference: nanmean fill, all-NaN -> 0
-        const bool all_nan = n_nan >= (float)a.crop;
-        const float fill = all_nan ? 0.f : (xc[0][1] + xc[1][1]) / ((float)a.crop - n_nan);
-        float m = 0.f;
-        for (int i = tid; i < seg_n; i += kCThreads) {
-          float d = yb[kCMargin + i];
-          if (all_nan) d = 0.f; else if (d != d) d = fill;
-          yb[kCMargin + i] = d;
-          m = fmaxf(m, fabsf(d));
-        }
-        amax = block_max_nan(m, sh.red_max, lane, warp);
-      }
-      if (a.pad_mode == 1) {   // reflect padding (librosa < 0.10); zero padding is the resident state
-        __syncthreads();
-        for (int k = tid; k < 2 * kCMargin + 128; k += kCThreads) {
-          const int idx = k < kCMargin ? k : seg_n + k;          // left margin | right margin
-          const int i = seg_lo + idx - kCMargin;                 // crop coordinate
-          const int src = i < 0 ? -i : (i >= a.crop ? 2 * (a.crop - 1) - i : -1);
-          const int sidx = src - seg_lo;
-          if (idx < kCYFloats) yb[idx] = (src >= 0 && sidx >= 0 && sidx < seg_n) ? yb[kCMargin + sidx] : 0.f;
-        }
-        __syncthreads();
-      }
-      // exact power-of-two pre-scale: amax * 2^e in [2^10, 2^11)
-      {
-        int ex = 0;
-        if (amax > 0.f && amax < __int_as_float(0x7f800000)) { frexpf(amax, &ex); e_j = 11 - ex; }
-        e_j = max(-60, min(60, e_j));
-      }
-      const float s = __int_as_float((127 + e_j) << 23);
-
-      if (j >= 1) c_mbar_wait(mma_bar, (j - 1) & 1);   // tile j-1 no longer reads the operand tiles
-      asm volatile("tcgen05.fence::after_thread_sync;" ::);
-
-      // operand build: thread = (frame, 32 fold indices); E = s(y[c+m] + y[c-m]), O = s(y[c+m] - y[c-m])
-      {
-        const float* yc = yb + kCMargin + (128 * h + t_frame) * a.hop - seg_lo;
-#pragma unroll 1
-        for (int o = 0; o < 4; ++o) {
-          const int m0 = 32 * grp + 8 * o;
-          float ev[8], ov[8];
-#pragma unroll
-          for (int q = 0; q < 8; ++q) {
-            const float yp = yc[m0 + q], yms = yc[-(m0 + q)] * s;
-            ev[q] = fmaf(yp, s, yms);
-            ov[q] = fmaf(yp, s, -yms);
-          }
-          uint4 eh, el, oh, ol;
-          c_split2(ev[0], ev[1], eh.x, el.x); c_split2(ev[2], ev[3], eh.y, el.y);
-          c_split2(ev[4], ev[5], eh.z, el.z); c_split2(ev[6], ev[7], eh.w, el.w);
-          c_split2(ov[0], ov[1], oh.x, ol.x); c_split2(ov[2], ov[3], oh.y, ol.y);
-          c_split2(ov[4], ov[5], oh.z, ol.z); c_split2(ov[6], ov[7], oh.w, ol.w);
-          const int off = c_umma_offset(t_frame, m0);
-          *reinterpret_cast<uint4*>(tiles + 0 * kCTileBytes + off) = eh;
-          *reinterpret_cast<uint4*>(tiles + 1 * kCTileBytes + off) = el;
-          *reinterpret_cast<uint4*>(tiles + 2 * kCTileBytes + off) = oh;
-          *reinterpret_cast<uint4*>(tiles + 3 * kCTileBytes + off) = ol;
-        }
-      }
-      // frames beyond the kept width (they only feed the pair maximum) become rows of a small
-      // second B operand: one (frame, fold index) element per thread
-      if (tid < n_extra * kFold) {
-        const int x = tid >> 6, m = tid & (kFold - 1);
-        const float* yc = yb + kCMargin + (a.n_time + x) * a.hop - seg_lo;
-        const float yp = yc[m], yms = yc[-m] * s;
-        const float e = fmaf(yp, s, yms), o = fmaf(yp, s, -yms);
-        const float eh = __uint_as_float(__float_as_uint(e) & 0xFFFFE000u);
-        const float oh = __uint_as_float(__float_as_uint(o) & 0xFFFFE000u);
-        const int off = c_umma_offset(x, m);
-        *reinterpret_cast<__half*>(xt + 0 * kCXTileBytes + off) = __float2half_rn(eh);
-        *reinterpret_cast<__half*>(xt + 1 * kCXTileBytes + off) = __float2half_rn(e - eh);
-        *reinterpret_cast<__half*>(xt + 2 * kCXTileBytes + off) = __float2half_rn(oh);
-        *reinterpret_cast<__half*>(xt + 3 * kCXTileBytes + off) = __float2half_rn(o - oh);
-      }
+  // ======================================================================= control warp group
+  // The register file is partitioned per scheduler (16 384 each): the control warp group gives
+  // its registers back so that the compute warps can hold their accumulators (setmaxnreg).
+  if (warp >= kWarps) {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 24;");
+   if (warp == kWarps) {
+    auto issue_load = [&](int j) {   // both electrode rows of pair j -> staging (TMA bulk copies)
+      int rec, chain;
+      const int pr = pair_of(j, rec, chain);
+      const float* base = a.eeg + rec * a.rec_stride + a.crop_off + seg_lo;
+      const uint32_t bytes = (uint32_t)seg_n * 4u;
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-      asm volatile("tcgen05.fence::before_thread_sync;" ::);
-      __syncthreads();
-      // MMA issue, spread over four warps (one per scheduler): Re, Im, extra Re, extra Im are
-      // independent accumulators; each issuing thread commits to the same mbarrier (count 4).
-      if (warp < 4 && lane == 0) {
+      c_mbar_expect_tx(load_bar, 2 * bytes);
+      c_bulk_g2s(c_smem_u32(stage), base + a.pair_a[pr] * a.ch_stride, bytes, load_bar);
+      c_bulk_g2s(c_smem_u32(stage + kCStageFloats), base + a.pair_b[pr] * a.ch_stride, bytes, load_bar);
+    };
+    if (lane == 0) issue_load(0);
+    c_mbar_wait(diff_bar, 0);                 // staging consumed by diff(0)
+    if (lane == 0 && J > 1) issue_load(1);
+    for (int j = 0; j <= J; ++j) {
+      if (j < J) {                            // ---- the MMA stream of tile j
+        c_mbar_wait(ops_bar, j & 1);
         asm volatile("tcgen05.fence::after_thread_sync;" ::);
-        uint32_t tab0 = c_smem_u32(tab), til0 = c_smem_u32(tiles), xt0 = c_smem_u32(xt);
-        // opaque to the optimiser: keeps the descriptors out of the loop-invariant (spilled) set
-        asm volatile("" : "+r"(tab0), "+r"(til0), "+r"(xt0));
-        const int part = warp & 1;
-        if (warp < 2 || n_extra > 0) {
-          const bool big = warp < 2;
-          // big: D[frame][bin] = tiles (A) x tables (B); extra: D'[bin][frame] = tables (A) x xt (B)
-          const uint32_t d = big ? tmem_base + (j & 1) * kCAccCols + part * kCBins
-                                 : tmem_base + kCXTmemCol + (j & 1) * 2 * kCXCols + part * kCXCols;
-          const uint32_t t_hi = tab0 + (2 * part) * kCTabBytes, t_lo = t_hi + kCTabBytes;
-          const uint32_t f_hi = big ? til0 + (2 * part) * kCTileBytes : xt0 + (2 * part) * kCXTileBytes;
-          const uint32_t f_lo = f_hi + (big ? kCTileBytes : kCXTileBytes);
-          const uint32_t idesc = big ? kCIdesc : kCIdescX;
-          uint32_t accum = 0;
+        if (lane == 0) {
+          uint32_t tab0 = c_smem_u32(tab), til0 = c_smem_u32(tiles), xt0 = c_smem_u32(xt);
 #pragma unroll 1
-          for (int term = 0; term < 3; ++term) {   // hi.hi + lo.hi + hi.lo  (frames x tables)
-            const uint32_t ff = term == 1 ? f_lo : f_hi, tt = term == 2 ? t_lo : t_hi;
-            const uint64_t fd = c_umma_desc(ff), td = c_umma_desc(tt);
+          for (int grp = 0; grp < (n_extra > 0 ? 4 : 2); ++grp) {   // Re, Im, extra Re, extra Im
+            const int part = grp & 1;
+            const bool big = grp < 2;
+            // big: D[frame][bin] = tiles (A) x tables (B); extra: D'[bin][frame] = tables (A) x xt (B)
+            const uint32_t d = big ? tmem_base + (j & 1) * kCAccCols + part * kCBins
+                                   : tmem_base + kCXTmemCol + (j & 1) * 2 * kCXCols + part * kCXCols;
+            const uint32_t t_hi = tab0 + (2 * part) * kCTabBytes, t_lo = t_hi + kCTabBytes;
+            const uint32_t f_hi = big ? til0 + (2 * part) * kCTileBytes : xt0 + (2 * part) * kCXTileBytes;
+            const uint32_t f_lo = f_hi + (big ? kCTileBytes : kCXTileBytes);
+            const uint32_t idesc = big ? kCIdesc : kCIdescX;
+            uint32_t accum = 0;
+#pragma unroll 1
+            for (int term = 0; term < 3; ++term) {   // hi.hi + lo.hi + hi.lo  (frames x tables)
+              const uint64_t fd = c_umma_desc(term == 1 ? f_lo : f_hi), td = c_umma_desc(term == 2 ? t_lo : t_hi);
 #pragma unroll
-            for (int ks = 0; ks < kFold / 16; ++ks) {
-              const uint64_t fdk = fd + (uint64_t)(ks * 16), tdk = td + (uint64_t)(ks * 16);
-              c_umma(d, big ? fdk : tdk, big ? tdk : fdk, accum, idesc);
-              accum = 1;
+              for (int ks = 0; ks < kFold / 16; ++ks) {
+                const uint64_t fdk = fd + (uint64_t)(ks * 16), tdk = td + (uint64_t)(ks * 16);
+                c_umma(d, big ? fdk : tdk, big ? tdk : fdk, accum, idesc);
+                accum = 1;
+              }
             }
           }
+          asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(mma_bar) : "memory");
         }
-        asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(mma_bar) : "memory");
+        __syncwarp();
+      }
+      if (j >= 1) {                           // ---- publish the maximum of tile j-1 to both CTAs
+        const int jt = j - 1;
+        c_mbar_wait(epi_bar, jt & 1);
+        if (lane == 0) {
+          float r_true = sh.w_vmax[jt & 1][0];   // per-warp log2 maxima, already in unscaled units
+          for (int w = 1; w < kWarps; ++w) r_true = fmaxf(r_true, sh.w_vmax[jt & 1][w]);
+          float* slot = &sh.xch[jt & 1][h];
+          *slot = r_true;
+          c_st_peer_f32(c_smem_u32(slot), peer, r_true);
+          const uint32_t xb = c_smem_u32(&sh.xch_bar[jt & 1]);
+          c_mbar_arrive_cluster(xb, (uint32_t)h);
+          c_mbar_arrive_cluster(xb, (uint32_t)peer);
+        }
+        __syncwarp();
+      }
+      if (j + 1 < J) {                        // ---- staging is free once diff(j+1) is done
+        c_mbar_wait(diff_bar, (j + 1) & 1);
+        if (lane == 0 && j + 2 < J) issue_load(j + 2);
       }
     }
-
-    float r_true = 0.f;
-    if (j >= 1) {
-      const int jt = j - 1;
-      if (j == J) c_mbar_wait(mma_bar, jt & 1);
-      asm volatile("tcgen05.fence::after_thread_sync;" ::);
-      float t_fold = t_prev;
-      if (jt % a.ppc == 0) {   // first pair of an item: write the finished one, start afresh
-        if (jt > 0) flush(jt - 1, t_prev);
+   }
+  } else {
+    if constexpr (NQ == 4) asm volatile("setmaxnreg.inc.sync.aligned.u32 112;");   // pool: 128 x (96 - 24) freed
+    else asm volatile("setmaxnreg.inc.sync.aligned.u32 240;");
+    // ============================================================================= compute warps
+    const int t_frame = tid & (kTileFrames - 1), part = tid >> 7;
+    auto cta_max_nan = [&](float v) {
+      v = warp_max_nan(v);
+      if (lane == 0) sh.red[warp] = v;
+      c_named_bar(1, kCompute);
+      float r = sh.red[0];
 #pragma unroll
-        for (int i = 0; i < 64; ++i) { acc[i] = 0.f; qprev[i] = 0.f; }
-        csum = 0.f;
-        t_fold = 0.f;
+      for (int w = 1; w < kWarps; ++w) r = max_nan(r, sh.red[w]);
+      c_named_bar(1, kCompute);
+      return r;
+    };
+    auto cta_sum = [&](float v) {
+      v = warp_sum(v);
+      if (lane == 0) sh.red[warp] = v;
+      c_named_bar(1, kCompute);
+      float r = 0.f;
+#pragma unroll
+      for (int w = 0; w < kWarps; ++w) r += sh.red[w];
+      c_named_bar(1, kCompute);
+      return r;
+    };
+    // difference of pair j's electrode rows into ybuf[j & 1]; per-warp max|y| (NaN if any NaN)
+    auto diff_pass = [&](int j) {
+      c_mbar_wait(load_bar, j & 1);
+      const float4* sa = reinterpret_cast<const float4*>(stage);
+      const float4* sb = reinterpret_cast<const float4*>(stage + kCStageFloats);
+      float4* yd = reinterpret_cast<float4*>(ybuf + (j & 1) * kCYFloats + kCMargin);
+      float amax = 0.f;
+      for (int i = tid; i < (seg_n >> 2); i += kCompute) {
+        const float4 x = sa[i], y = sb[i];
+        const float4 d = make_float4(x.x - y.x, x.y - y.y, x.z - y.z, x.w - y.w);
+        yd[i] = d;
+        amax = max_nan(max_nan(amax, fabsf(d.x)), max_nan(fabsf(d.y), max_nan(fabsf(d.z), fabsf(d.w))));
       }
-      const uint32_t lane_addr = tmem_base + ((uint32_t)(32 * (warp & 3)) << 16) + (jt & 1) * kCAccCols;
-      float vmax = 0.f;
-      float re[8], im[8];
+      amax = warp_max_nan(amax);
+      if (lane == 0) sh.w_amax[j & 1][warp] = amax;
+      __syncwarp();
+      if (lane == 0) c_mbar_arrive(diff_bar);
+    };
+
+    float acc[kMels], qprev[kMels];
+#pragma unroll
+    for (int i = 0; i < kMels; ++i) { acc[i] = 0.f; qprev[i] = 0.f; }
+    float csum = 0.f;
+    int e_jm1 = 0, e_jm2 = 0;
+
+    auto flush = [&](int j_last, float t_fold) {   // write the item whose last tile is j_last
+      int rec, chain;
+      pair_of(j_last, rec, chain);
+      float* o = a.out + (((long long)rec * a.n_mels + kMels * part) * a.n_time + 128 * h + t_frame) * a.n_chains + chain;
+      const int mstride = a.n_time * a.n_chains;
+#pragma unroll
+      for (int i = 0; i < kMels; ++i)
+        o[i * mstride] = fmaf(a.out_gain, acc[i] + fmaxf(qprev[i], t_fold) - csum, a.out_bias);
+    };
+    auto fold_constants = [&](int n, float& t_out) {   // exchange n: threshold and reference of tile n
+      c_mbar_wait_cluster(c_smem_u32(&sh.xch_bar[n & 1]), (uint32_t)((n >> 1) & 1));
+      const float r_pair = fmaxf(fmaxf(sh.xch[n & 1][0], sh.xch[n & 1][1]), a.log2_amin);
+      const float off = 2.f * (float)e_jm2;
+      t_out = fmaxf(a.log2_amin, r_pair - a.top_log2) + off;
+      csum += r_pair + off;
+    };
+
+    diff_pass(0);
+    for (int j = 0; j <= J; ++j) {
+      int e_j = 0;
+      if (j < J) {
+        c_named_bar(1, kCompute);   // diff(j) is complete in every warp: y and w_amax are final
+        float* yb = ybuf + (j & 1) * kCYFloats;
+        float amax = sh.w_amax[j & 1][0];
+#pragma unroll
+        for (int w = 1; w < kWarps; ++w) amax = max_nan(amax, sh.w_amax[j & 1][w]);
+        if (amax != amax) {
+          // NaN samples (rare).  cfg_utils.py:380-385 on the difference: nanmean over the whole
+          // crop, all-NaN -> 0.  Each CTA re-reads both full rows, so no exchange is needed and
+          // both halves get the identical fill value.
+          int rec, chain;
+          const int pr = pair_of(j, rec, chain);
+          const float* ra = a.eeg + rec * a.rec_stride + a.pair_a[pr] * a.ch_stride + a.crop_off;
+          const float* rb = a.eeg + rec * a.rec_stride + a.pair_b[pr] * a.ch_stride + a.crop_off;
+          float s_ = 0.f, c_ = 0.f;
+          for (int i = tid; i < a.crop; i += kCompute) {
+            const float d = __ldg(ra + i) - __ldg(rb + i);
+            if (d != d) c_ += 1.f; else s_ += d;
+          }
+          s_ = cta_sum(s_);
+          c_ = cta_sum(c_);
+          const bool all_nan = c_ >= (float)a.crop;
+          const float fill = all_nan ? 0.f : s_ / ((float)a.crop - c_);
+          float m = 0.f;
+          for (int i = tid; i < seg_n; i += kCompute) {
+            float d = yb[kCMargin + i];
+            if (all_nan) d = 0.f; else if (d != d) d = fill;
+            yb[kCMargin + i] = d;
+            m = fmaxf(m, fabsf(d));
+          }
+          amax = cta_max_nan(m);
+        }
+        if (a.pad_mode == 1) {   // reflect padding (librosa < 0.10); zero padding is the resident state
+          for (int k = tid; k < 2 * kCMargin + 128; k += kCompute) {
+            const int idx = k < kCMargin ? k : seg_n + k;          // left margin | right margin
+            const int i = seg_lo + idx - kCMargin;                 // crop coordinate
+            const int src = i < 0 ? -i : (i >= a.crop ? 2 * (a.crop - 1) - i : -1);
+            const int sidx = src - seg_lo;
+            if (idx < kCYFloats) yb[idx] = (src >= 0 && sidx >= 0 && sidx < seg_n) ? yb[kCMargin + sidx] : 0.f;
+          }
+          c_named_bar(1, kCompute);
+        }
+        {   // exact power-of-two pre-scale: amax * 2^e in [2^10, 2^11)
+          int ex = 0;
+          if (amax > 0.f && amax < __int_as_float(0x7f800000)) { frexpf(amax, &ex); e_j = 11 - ex; }
+          e_j = max(-60, min(60, e_j));
+        }
+        const float s = __int_as_float((127 + e_j) << 23);
+
+        if (j >= 1) c_mbar_wait(mma_bar, (j - 1) & 1);   // tile j-1 is done: operand tiles are free
+        asm volatile("tcgen05.fence::after_thread_sync;" ::);
+        {   // operand build: E = s(y[c+m] + y[c-m]), O = s(y[c+m] - y[c-m]) as fp16 hi/lo
+          const float* yc = yb + kCMargin + (128 * h + t_frame) * a.hop - seg_lo;
+#pragma unroll
+          for (int o = 0; o < kOct; ++o) {
+            const int m0 = (64 / NQ) * part + 8 * o;
+            float ev[8], ov[8];
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+              const float yp = yc[m0 + q], yms = yc[-(m0 + q)] * s;
+              ev[q] = fmaf(yp, s, yms);
+              ov[q] = fmaf(yp, s, -yms);
+            }
+            uint4 eh, el, oh, ol;
+            c_split2(ev[0], ev[1], eh.x, el.x); c_split2(ev[2], ev[3], eh.y, el.y);
+            c_split2(ev[4], ev[5], eh.z, el.z); c_split2(ev[6], ev[7], eh.w, el.w);
+            c_split2(ov[0], ov[1], oh.x, ol.x); c_split2(ov[2], ov[3], oh.y, ol.y);
+            c_split2(ov[4], ov[5], oh.z, ol.z); c_split2(ov[6], ov[7], oh.w, ol.w);
+            const int off = c_umma_offset(t_frame, m0);
+            *reinterpret_cast<uint4*>(tiles + 0 * kCTileBytes + off) = eh;
+            *reinterpret_cast<uint4*>(tiles + 1 * kCTileBytes + off) = el;
+            *reinterpret_cast<uint4*>(tiles + 2 * kCTileBytes + off) = oh;
+            *reinterpret_cast<uint4*>(tiles + 3 * kCTileBytes + off) = ol;
+          }
+        }
+        // frames beyond the kept width (they only feed the pair maximum) are rows of a small
+        // second operand: one (frame, fold index) element per thread
+        if (tid < n_extra * kFold) {
+          const int x = tid >> 6, m = tid & (kFold - 1);
+          const float* yc = yb + kCMargin + (a.n_time + x) * a.hop - seg_lo;
+          const float yp = yc[m], yms = yc[-m] * s;
+          const float e = fmaf(yp, s, yms), o = fmaf(yp, s, -yms);
+          const float eh = __uint_as_float(__float_as_uint(e) & 0xFFFFE000u);
+          const float oh = __uint_as_float(__float_as_uint(o) & 0xFFFFE000u);
+          const int off = c_umma_offset(x, m);
+          *reinterpret_cast<__half*>(xt + 0 * kCXTileBytes + off) = __float2half_rn(eh);
+          *reinterpret_cast<__half*>(xt + 1 * kCXTileBytes + off) = __float2half_rn(e - eh);
+          *reinterpret_cast<__half*>(xt + 2 * kCXTileBytes + off) = __float2half_rn(oh);
+          *reinterpret_cast<__half*>(xt + 3 * kCXTileBytes + off) = __float2half_rn(o - oh);
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        asm volatile("tcgen05.fence::before_thread_sync;" ::);
+        __syncwarp();
+        if (lane == 0) c_mbar_arrive(ops_bar);
+      }
+
+      if (j >= 1) {   // ---- epilogue of tile j-1 (the tensor pipe is busy with tile j meanwhile)
+        const int jt = j - 1;
+        if (j == J) c_mbar_wait(mma_bar, jt & 1);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::);
+        float t_prev = 0.f;   // clip threshold of tile j-2, in that tile's scaled log2 units
+        if (j >= 2) fold_constants(j - 2, t_prev);
+        float t_fold = t_prev;
+        if (jt % a.ppc == 0) {   // first pair of an item: write the finished one, start afresh
+          if (jt > 0) flush(jt - 1, t_prev);
+#pragma unroll
+          for (int i = 0; i < kMels; ++i) { acc[i] = 0.f; qprev[i] = 0.f; }
+          csum = 0.f;
+          t_fold = 0.f;
+        }
+        const uint32_t lane_addr = tmem_base + ((uint32_t)(32 * (warp & 3)) << 16) + (jt & 1) * kCAccCols;
+        float vmax = 0.f;
+        float re[8], im[8];
 #define CH_POW(s, i) const float p##s = fmaf(re[i], re[i], im[i] * im[i]);
 #define CH_MEL_TAIL(i)                       \
   vmax = fmaxf(vmax, v);                     \
@@ -507,66 +562,61 @@ melspec_chain_kernel(const ChainArgs a) {
   qprev[i] = c_lg2(v);
 #define CH_MEL1(i, sa, w0) { const float v = (w0) * p##sa; CH_MEL_TAIL(i) }
 #define CH_MEL2(i, sa, sb, w0, w1) { const float v = fmaf(w1, p##sb, (w0) * p##sa); CH_MEL_TAIL(i) }
-      if (grp == 0) {
-#define CH_LOAD(c) c_tmem_ld8x2(lane_addr + MELGEN_COL0_H0 + 8 * (c), lane_addr + kCBins + MELGEN_COL0_H0 + 8 * (c), re, im);
-        MELGEN_EPILOGUE_H0(CH_LOAD, CH_POW, CH_MEL1, CH_MEL2)
+#define CH_LOAD(c) c_tmem_ld8x2(lane_addr + col0 + 8 * (c), lane_addr + kCBins + col0 + 8 * (c), re, im);
+#define CH_PART(TAG)                                                \
+  {                                                                 \
+    constexpr int col0 = MELGEN_COL0_##TAG;                         \
+    MELGEN_EPILOGUE_##TAG(CH_LOAD, CH_POW, CH_MEL1, CH_MEL2)        \
+  }
+        if constexpr (NQ == 2) {
+          if (part == 0) CH_PART(P2_0) else CH_PART(P2_1)
+        } else {
+          if (part == 0) CH_PART(P4_0) else if (part == 1) CH_PART(P4_1) else if (part == 2) CH_PART(P4_2) else CH_PART(P4_3)
+        }
+#undef CH_PART
 #undef CH_LOAD
-      } else {
-#define CH_LOAD(c) c_tmem_ld8x2(lane_addr + MELGEN_COL0_H1 + 8 * (c), lane_addr + kCBins + MELGEN_COL0_H1 + 8 * (c), re, im);
-        MELGEN_EPILOGUE_H1(CH_LOAD, CH_POW, CH_MEL1, CH_MEL2)
-#undef CH_LOAD
-      }
 #undef CH_POW
 #undef CH_MEL_TAIL
 #undef CH_MEL1
 #undef CH_MEL2
-      asm volatile("tcgen05.fence::before_thread_sync;" ::);
 
-      // extra frames: lane = bin slot, column = frame; power -> shared -> mel maximum
-      if (n_extra > 0) {
-        if (warp < 4) {
+        // extra frames: lane = bin slot, column = frame; power -> shared -> mel maximum (warps 0-3)
+        if (n_extra > 0 && part == 0) {
           const uint32_t xaddr = tmem_base + ((uint32_t)(32 * warp) << 16) + kCXTmemCol + (jt & 1) * 2 * kCXCols;
           float xr[4], xi[4];
           c_tmem_ld4(xaddr, xr);
           c_tmem_ld4(xaddr + kCXCols, xi);
 #pragma unroll
           for (int x = 0; x < kCMaxExtra; ++x) sh.px[x * 128 + tid] = fmaf(xr[x], xr[x], xi[x] * xi[x]);
+          c_named_bar(2, 128);
+          for (int i = tid; i < n_extra * a.n_mels; i += 128) {
+            const int x = i / a.n_mels, m = i % a.n_mels;
+            const int k0 = sh.mel_k0[m];
+            vmax = fmaxf(vmax, fmaf(sh.mel_w1[m], sh.px[x * 128 + k0 + 1], sh.mel_w0[m] * sh.px[x * 128 + k0]));
+          }
         }
+        vmax = warp_max_nan(vmax);
+        if (lane == 0) sh.w_vmax[jt & 1][warp] = c_lg2(vmax) - 2.f * (float)e_jm1;
         asm volatile("tcgen05.fence::before_thread_sync;" ::);
-        __syncthreads();
-        for (int i = tid; i < n_extra * a.n_mels; i += kCThreads) {
-          const int x = i / a.n_mels, m = i % a.n_mels;
-          const int k0 = sh.mel_k0[m];
-          vmax = fmaxf(vmax, fmaf(sh.mel_w1[m], sh.px[x * 128 + k0 + 1], sh.mel_w0[m] * sh.px[x * 128 + k0]));
-        }
+        __syncwarp();
+        if (lane == 0) c_mbar_arrive(epi_bar);
       }
-      const float vm = block_max_nan(vmax, sh.red_v, lane, warp);
-      r_true = c_lg2(vm) - 2.f * (float)e_jm1;
+
+      if (j + 1 < J) diff_pass(j + 1);
+      e_jm2 = e_jm1;
+      e_jm1 = e_j;
     }
 
-    if (j + 1 < J) {
-      diff_pass(j + 1);   // ends with a block barrier: staging is free again
-      if (tid == 0 && j + 2 < J) issue_load(j + 2);
-    }
-    publish(j & 1, r_true);
-    e_jm2 = e_jm1;
-    e_jm1 = e_j;
+    // ---- the last pair's maximum has been exchanged: write the last item
+    float t_last;
+    fold_constants(J - 1, t_last);
+    flush(J - 1, t_last);
   }
 
-  // ---- drain: the last pair's maximum has been exchanged; write the last item
-  c_cluster_wait();
-  {
-    const float(*xc)[4] = sh.xch[J & 1];
-    const float r_pair = fmaxf(fmaxf(xc[0][0], xc[1][0]), a.log2_amin);
-    const float off = 2.f * (float)e_jm2;
-    csum += r_pair + off;
-    flush(J - 1, fmaxf(a.log2_amin, r_pair - a.top_log2) + off);
-  }
   asm volatile("tcgen05.fence::before_thread_sync;" ::);
   __syncthreads();
   if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512));
-  // the peer may still be writing into this CTA's shared memory until it has passed the last wait
-  c_cluster_arrive();
+  c_cluster_arrive();   // nobody exits while its peer may still write or arrive remotely
   c_cluster_wait();
 }
 
@@ -636,7 +686,9 @@ int melspec_chain_launch(const MelArgs& m, const eegspec_mel_params& p, long lon
   if (dev < 0 || dev >= 64) return EEGSPEC_EUNSUPPORTED;
   const size_t smem = melspec_chain_smem_bytes();
   if (!configured[dev]) {
-    cudaError_t e = cudaFuncSetAttribute(melspec_chain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = cudaFuncSetAttribute(melspec_chain_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return (int)e;
+    e = cudaFuncSetAttribute(melspec_chain_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return (int)e;
     e = cudaDeviceGetAttribute(&sm_count[dev], cudaDevAttrMultiProcessorCount, dev);
     if (e != cudaSuccess) return (int)e;
@@ -646,7 +698,9 @@ int melspec_chain_launch(const MelArgs& m, const eegspec_mel_params& p, long lon
   if (clusters < 1) clusters = 1;
   if (clusters > a.n_items) clusters = a.n_items;
   if ((a.n_items + clusters - 1) / clusters * a.ppc > (1LL << 30)) return EEGSPEC_EUNSUPPORTED;
-  melspec_chain_kernel<<<(unsigned)(2 * clusters), kCThreads, smem, st>>>(a);
+  static const int nq = [] { const char* v = getenv("EEGSPEC_CHAIN_NQ"); return (v && v[0] == '2') ? 2 : 4; }();
+  if (nq == 2) melspec_chain_kernel<2><<<(unsigned)(2 * clusters), 128 * 2 + 128, smem, st>>>(a);
+  else melspec_chain_kernel<4><<<(unsigned)(2 * clusters), 128 * 4 + 128, smem, st>>>(a);
   count_launch();
   return (int)cudaGetLastError();
 }
