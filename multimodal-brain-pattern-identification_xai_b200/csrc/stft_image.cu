@@ -19,6 +19,7 @@
 // the image is written once, nothing else touches DRAM.
 #include "common.cuh"
 #include "internal.h"
+#include "stft_thread_fft.cuh"
 
 namespace eegspec {
 
@@ -211,12 +212,50 @@ __device__ __forceinline__ void fft_phase(const StftArgs& a, const float* __rest
   }
 }
 
+// Phase 1 for nperseg <= 64: one thread per frame, everything in registers
+// (stft_thread_fft.cuh).  Interior frames of 16-byte aligned rows are fetched as float4.
+template <int LOG2N, int STRIDE>
+__device__ __forceinline__ void fft_thread_phase(const StftArgs& a, const float* __restrict__ xrow,
+                                                 float* S) {
+  constexpr int N = 1 << LOG2N;
+  const bool vec_ok = !a.gather && ((a.hop | a.half) & 3) == 0 &&
+                      (reinterpret_cast<uintptr_t>(xrow) & 15) == 0;
+  for (int slot = threadIdx.x; slot < a.n_slots; slot += blockDim.x) {
+    long long frame = slot;
+    if (a.gather) {
+      int rem;
+      bracket_of(a, slot >> 1, frame, rem);
+      frame += (slot & 1);
+    }
+    const long long s0 = frame * a.hop - a.half;
+    float v[N];
+    if (vec_ok && s0 >= 0 && s0 + N <= a.L) {
+      const float4* src = reinterpret_cast<const float4*>(xrow + s0);
+#pragma unroll
+      for (int i = 0; i < N / 4; ++i) {
+        const float4 t = __ldg(src + i);
+        v[4 * i] = t.x; v[4 * i + 1] = t.y; v[4 * i + 2] = t.z; v[4 * i + 3] = t.w;
+      }
+    } else {   // SciPy's zero boundary extension / end padding
+#pragma unroll
+      for (int i = 0; i < N; ++i) {
+        const long long n = s0 + i;
+        v[i] = (n >= 0 && n < a.L) ? __ldg(xrow + n) : 0.f;
+      }
+    }
+    float* Sc = S + (long long)slot * STRIDE;
+    const long long kstride = (long long)a.n_pad * STRIDE;
+    frame_fft_mag<LOG2N>(v, [&](int k, float mag) { Sc[k * kstride] = log1p_pos(mag); });
+  }
+}
+
 constexpr int kStftMaxThreads = 512;
+constexpr int kStftThreadFftMax = 320;   // thread-per-frame path: 2 CTAs of 320 threads x <= 102 registers
 
 // MODE 0: knots in shared memory (the normal case); 1: knots in a global workspace slice
 // (very long rows); 2: log-magnitude only, knots written straight to the output.
 template <int LOG2N, int MODE>
-__global__ void __launch_bounds__(kStftMaxThreads, (LOG2N <= 7 ? 2 : 1))
+__global__ void __launch_bounds__((LOG2N <= 6 ? kStftThreadFftMax : kStftMaxThreads), (LOG2N <= 7 ? 2 : 1))
 stft_image_kernel(const StftArgs a) {
   constexpr int N = 1 << LOG2N, P = N / 2, F = P + 1;
   constexpr int LPF = P < 32 ? P : 32;
@@ -224,12 +263,13 @@ stft_image_kernel(const StftArgs a) {
   constexpr int STRIDE = MODE == 2 ? 1 : 2;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int nthreads = blockDim.x, nwarps = nthreads >> 5;
+  constexpr bool kThreadFft = LOG2N <= 6;   // tables live in the instruction stream
   float2* tw = reinterpret_cast<float2*>(smem_raw);                 // P/2 (>=1)
-  float2* utw = tw + (P / 2 > 0 ? P / 2 : 1);                       // P
-  float2* zs = utw + P;                                             // warps * FPW * P
-  float2* ends = zs + nwarps * FPW * P;                             // one per segment when ends_only
+  float2* utw = tw + (kThreadFft ? 0 : (P / 2 > 0 ? P / 2 : 1));    // P
+  float2* zs = utw + (kThreadFft ? 0 : P);                          // warps * FPW * P
+  float2* ends = zs + (kThreadFft ? 0 : nwarps * FPW * P);          // one per segment when ends_only
   float* win = reinterpret_cast<float*>(ends + (a.ends_only ? a.n_items : 0));  // N
-  int* rowflag = reinterpret_cast<int*>(win + N);                   // F + 1 (NaN rows, any)
+  int* rowflag = reinterpret_cast<int*>(win + (kThreadFft ? 0 : N));  // F + 1 (NaN rows, any)
   float* S_sm = reinterpret_cast<float*>(rowflag + F + 1 + ((F + 1) & 1));      // F*n_pad*STRIDE
 
   const long long row = blockIdx.x / a.split;
@@ -243,12 +283,14 @@ stft_image_kernel(const StftArgs a) {
   else S = S_sm;
 
   // Tables.  Periodic Hann scaled by 1/sum(w) = 2/N (scipy scaling='spectrum', mode 'stft').
-  for (int j = tid; j < N; j += nthreads)
-    win[j] = (0.5f - 0.5f * cospif(2.0f * j / N)) * (2.0f / N);
-  for (int k = tid; k < P / 2; k += nthreads)
-    tw[k] = make_float2(cospif(2.0f * k / P), -sinpif(2.0f * k / P));
-  for (int k = tid; k < P; k += nthreads)
-    utw[k] = make_float2(cospif(2.0f * k / N), sinpif(2.0f * k / N));
+  if constexpr (!kThreadFft) {
+    for (int j = tid; j < N; j += nthreads)
+      win[j] = (0.5f - 0.5f * cospif(2.0f * j / N)) * (2.0f / N);
+    for (int k = tid; k < P / 2; k += nthreads)
+      tw[k] = make_float2(cospif(2.0f * k / P), -sinpif(2.0f * k / P));
+    for (int k = tid; k < P; k += nthreads)
+      utw[k] = make_float2(cospif(2.0f * k / N), sinpif(2.0f * k / N));
+  }
   if constexpr (MODE != 2) {
     for (int f = tid; f <= F; f += nthreads) rowflag[f] = 0;
     // First and last output column of every linear segment, as (knot slot, fraction): the
@@ -278,14 +320,18 @@ stft_image_kernel(const StftArgs a) {
   }
   __syncthreads();
 
-  fft_phase<LOG2N, STRIDE>(a, xrow, S, win, tw, utw, zs);
-  __syncthreads();
-
-  for (int s = tid; s < a.n_slots; s += nthreads) {
-    float* p = S + ((long long)P * a.n_pad + s) * STRIDE;
-    *p = log1p_pos(*p);
+  if constexpr (kThreadFft) {
+    fft_thread_phase<LOG2N, STRIDE>(a, xrow, S);
+    if constexpr (MODE == 2) return;
+  } else {
+    fft_phase<LOG2N, STRIDE>(a, xrow, S, win, tw, utw, zs);
+    __syncthreads();
+    for (int s = tid; s < a.n_slots; s += nthreads) {
+      float* p = S + ((long long)P * a.n_pad + s) * STRIDE;
+      *p = log1p_pos(*p);
+    }
+    if constexpr (MODE == 2) return;
   }
-  if constexpr (MODE == 2) return;
   __syncthreads();
 
   // Phase 2: per-frequency min/max of the interpolated row; then every knot becomes the pair
@@ -384,11 +430,13 @@ static size_t stft_fixed_smem(int nperseg, int threads, long long n_ends) {
   const int N = nperseg, P = N / 2, F = P + 1;
   const int LPF = P < 32 ? P : 32, FPW = 32 / LPF;
   size_t b = 0;
-  b += sizeof(float2) * (P / 2 > 0 ? P / 2 : 1);
-  b += sizeof(float2) * P;
-  b += sizeof(float2) * (threads / 32) * FPW * P;
+  if (N > 64) {   // the thread-per-frame path keeps no tables in shared memory
+    b += sizeof(float2) * (P / 2 > 0 ? P / 2 : 1);
+    b += sizeof(float2) * P;
+    b += sizeof(float2) * (threads / 32) * FPW * P;
+    b += sizeof(float) * N;
+  }
   b += sizeof(float2) * n_ends;
-  b += sizeof(float) * N;
   b += sizeof(int) * (F + 1 + ((F + 1) & 1));
   return b;
 }
@@ -448,7 +496,11 @@ static StftLaunchShape stft_shape(long long rows, int nperseg, const eegspec_stf
   // still keep 32 warps resident.
   s.threads = 256;
   size_t fixed = stft_fixed_smem(nperseg, s.threads, s.ends_only ? s.n_items : 0);
-  if (fixed + s_bytes > 54 * 1024) {
+  if (nperseg <= 64) {
+    // thread-per-frame FFT: one thread per slot up to the register-bound CTA size
+    long long t = (pl.n_slots + 31) / 32 * 32;
+    s.threads = (int)(t < 128 ? 128 : (t > kStftThreadFftMax ? kStftThreadFftMax : t));
+  } else if (fixed + s_bytes > 54 * 1024) {
     s.threads = kStftMaxThreads;
     fixed = stft_fixed_smem(nperseg, s.threads, s.ends_only ? s.n_items : 0);
   }
@@ -457,7 +509,8 @@ static StftLaunchShape stft_shape(long long rows, int nperseg, const eegspec_stf
   s.ws_per_cta = s.use_ws ? s_bytes : 0;
   // Small batches: slice the columns of a row over several CTAs so that all 148 SMs write.
   int resident = (int)((220 * 1024) / (s.smem + 1024));
-  if (resident > 1024 / s.threads) resident = 1024 / s.threads;   // 64 registers per thread
+  const int reg_threads = nperseg <= 64 ? 640 : 1024;             // ~100 | 64 registers per thread
+  if (resident > reg_threads / s.threads) resident = reg_threads / s.threads;
   if (resident < 1) resident = 1;
   const long long want = 148LL * resident;
   long long split = rows >= want ? 1 : (want + rows - 1) / rows;
@@ -585,7 +638,7 @@ int stft_logmag_launch(const float* x, long long rows, long long length, long lo
   a.out_cols = 4;
   a.D = 3;
   a.inv_d = 1.f / 3.f;
-  return dispatch(nperseg, a, rows, stft_fixed_smem(nperseg, 256, 0), 256, st);
+  return dispatch(nperseg, a, rows, stft_fixed_smem(nperseg, 256, 0), 256, st);   // 256 <= kStftThreadFftMax
 }
 
 }  // namespace eegspec
