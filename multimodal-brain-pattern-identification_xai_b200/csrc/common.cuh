@@ -61,6 +61,13 @@ __device__ __forceinline__ float sqrt_pos(float p) {
   return p > 0.f ? r : p;
 }
 
+// sqrt.approx (one MUFU, relative error 2^-23, sqrt(0) = 0, NaN propagates)
+__device__ __forceinline__ float sqrt_mufu(float p) {
+  float r;
+  asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(p));
+  return r;
+}
+
 __device__ __forceinline__ float2 cmul(float2 a, float2 b) {
   return make_float2(fmaf(a.x, b.x, -a.y * b.y), fmaf(a.x, b.y, a.y * b.x));
 }

@@ -270,7 +270,9 @@ stft_image_kernel(const StftArgs a) {
   float2* ends = zs + (kThreadFft ? 0 : nwarps * FPW * P);          // one per segment when ends_only
   float* win = reinterpret_cast<float*>(ends + (a.ends_only ? a.n_items : 0));  // N
   int* rowflag = reinterpret_cast<int*>(win + (kThreadFft ? 0 : N));  // F + 1 (NaN rows, any)
-  float* S_sm = reinterpret_cast<float*>(rowflag + F + 1 + ((F + 1) & 1));      // F*n_pad*STRIDE
+  float* part_lo = reinterpret_cast<float*>(rowflag + F + 1 + ((F + 1) & 1));   // nthreads: partial row minima
+  float* part_hi = part_lo + nthreads;                              // nthreads: partial row maxima
+  float* S_sm = part_hi + nthreads;                                 // F*n_pad*STRIDE
 
   const long long row = blockIdx.x / a.split;
   const int part = blockIdx.x % a.split;
@@ -303,8 +305,8 @@ stft_image_kernel(const StftArgs a) {
       const int per = (nm1 + nthreads - 1) / nthreads;
       const int seg0 = tid * per, seg1 = min(nm1, seg0 + per);
       if (seg0 < seg1) {
-        const int dq = D / nm1, dr = D % nm1;
-        int q = (int)(((long long)seg0 * D) / nm1), r = (int)(((long long)seg0 * D) % nm1);
+        const int dq = (int)((unsigned)D / (unsigned)nm1), dr = D - dq * nm1;
+        int q = (int)((unsigned)(seg0 * D) / (unsigned)nm1), r = seg0 * D - q * nm1;   // seg0 * D < 2^31
         int jf = q + (r ? 1 : 0);                       // first column of seg0
         for (int seg = seg0; seg < seg1; ++seg) {
           q += dq; r += dr;
@@ -337,6 +339,49 @@ stft_image_kernel(const StftArgs a) {
   // Phase 2: per-frequency min/max of the interpolated row; then every knot becomes the pair
   // {normalised value, normalised delta to the next knot} so that phase 3 is one FFMA per pixel.
   const long long nm1 = a.n_frames - 1;
+  if (a.ends_only && nthreads >= F) {
+    // Up-sampling (the usual case).  Thread = (frequency row f, run of consecutive segments):
+    // running min / max in two registers, lanes of a warp on consecutive rows (conflict-free:
+    // the knot row pitch is an odd number of float2).
+    float2* S2 = reinterpret_cast<float2*>(S);
+    const int nseg = a.n_items, groups = nthreads / F;
+    const int chunk = (nseg + groups - 1) / groups;
+    const int f = tid % F, c = tid / F;
+    const int seg0 = min(nseg, c * chunk), seg1 = c < groups ? min(nseg, seg0 + chunk) : seg0;
+    float2* K = S2 + (long long)f * a.n_pad;
+    float lo = __int_as_float(0x7f800000), hi = __int_as_float(0xff800000);
+    if (seg0 < seg1) {
+      float s0 = K[seg0].x;
+#pragma unroll 4
+      for (int seg = seg0; seg < seg1; ++seg) {
+        const float2 e = ends[seg];                 // fractions of the first / last column
+        const float s1 = K[seg + 1].x, d = s1 - s0;
+        const float va = fmaf(d, e.x, s0), vb = fmaf(d, e.y, s0);
+        lo = min_nan(lo, min_nan(va, vb));
+        hi = max_nan(hi, max_nan(va, vb));
+        K[seg].y = d;
+        s0 = s1;
+      }
+      if (seg1 == nseg) K[nseg].y = 0.f;
+    }
+    part_lo[tid] = lo;
+    part_hi[tid] = hi;
+    __syncthreads();
+    if (seg0 < seg1) {
+      for (int g = 0; g < groups; ++g) {
+        lo = min_nan(lo, part_lo[g * F + f]);
+        hi = max_nan(hi, part_hi[g * F + f]);
+      }
+      const float inv = 1.0f / (hi - lo + a.eps);
+      if (c == 0 && !(inv == inv)) { rowflag[f] = 1; rowflag[F] = 1; }
+      const int last = seg1 == nseg ? nseg + 1 : seg1;
+#pragma unroll 4
+      for (int seg = seg0; seg < last; ++seg) {
+        const float2 k = K[seg];
+        K[seg] = make_float2((k.x - lo) * inv, k.y * inv);
+      }
+    }
+  } else
   for (int f = warp; f < F; f += nwarps) {
     float* Sf = S + (long long)f * a.n_pad * STRIDE;
     float lo = __int_as_float(0x7f800000), hi = __int_as_float(0xff800000);
@@ -438,6 +483,7 @@ static size_t stft_fixed_smem(int nperseg, int threads, long long n_ends) {
   }
   b += sizeof(float2) * n_ends;
   b += sizeof(int) * (F + 1 + ((F + 1) & 1));
+  b += sizeof(float) * 2 * threads;   // partial row minima / maxima
   return b;
 }
 
@@ -500,6 +546,7 @@ static StftLaunchShape stft_shape(long long rows, int nperseg, const eegspec_stf
     // thread-per-frame FFT: one thread per slot up to the register-bound CTA size
     long long t = (pl.n_slots + 31) / 32 * 32;
     s.threads = (int)(t < 128 ? 128 : (t > kStftThreadFftMax ? kStftThreadFftMax : t));
+    fixed = stft_fixed_smem(nperseg, s.threads, s.ends_only ? s.n_items : 0);
   } else if (fixed + s_bytes > 54 * 1024) {
     s.threads = kStftMaxThreads;
     fixed = stft_fixed_smem(nperseg, s.threads, s.ends_only ? s.n_items : 0);

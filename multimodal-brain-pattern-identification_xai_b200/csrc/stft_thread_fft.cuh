@@ -103,10 +103,10 @@ __device__ __forceinline__ void frame_fft_mag(const float (&v)[1 << LOG2N], Emit
     constexpr float c = (float)cos64(k * TS), s = (float)sin64(k * TS);   // w^k = c - i s
     const float tr = fmaf(c, di, -s * dr), ti = -fmaf(c, dr, s * di);
     const float xr = sr + tr, xi = si + ti;
-    emit(k, sqrt_pos(fmaf(xr, xr, xi * xi)));
+    emit(k, sqrt_mufu(fmaf(xr, xr, xi * xi)));
     if constexpr (k != P - k) {
       const float yr = sr - tr, yi = si - ti;
-      emit(P - k, sqrt_pos(fmaf(yr, yr, yi * yi)));
+      emit(P - k, sqrt_mufu(fmaf(yr, yr, yi * yi)));
     }
   });
 }
