@@ -214,38 +214,50 @@ __device__ __forceinline__ void fft_phase(const StftArgs& a, const float* __rest
 
 // Phase 1 for nperseg <= 64: one thread per frame, everything in registers
 // (stft_thread_fft.cuh).  Interior frames of 16-byte aligned rows are fetched as float4.
-template <int LOG2N, int STRIDE>
-__device__ __forceinline__ void fft_thread_phase(const StftArgs& a, const float* __restrict__ xrow,
-                                                 float* S) {
+template <int LOG2N>
+__device__ __forceinline__ void frame_fetch(const StftArgs& a, const float* __restrict__ xrow, int slot,
+                                            float (&v)[1 << LOG2N]) {
   constexpr int N = 1 << LOG2N;
   const bool vec_ok = !a.gather && ((a.hop | a.half) & 3) == 0 &&
                       (reinterpret_cast<uintptr_t>(xrow) & 15) == 0;
-  for (int slot = threadIdx.x; slot < a.n_slots; slot += blockDim.x) {
-    long long frame = slot;
-    if (a.gather) {
-      int rem;
-      bracket_of(a, slot >> 1, frame, rem);
-      frame += (slot & 1);
-    }
-    const long long s0 = frame * a.hop - a.half;
-    float v[N];
-    if (vec_ok && s0 >= 0 && s0 + N <= a.L) {
-      const float4* src = reinterpret_cast<const float4*>(xrow + s0);
+  long long frame = slot;
+  if (a.gather) {
+    int rem;
+    bracket_of(a, slot >> 1, frame, rem);
+    frame += (slot & 1);
+  }
+  const long long s0 = frame * a.hop - a.half;
+  if (vec_ok && s0 >= 0 && s0 + N <= a.L) {
+    const float4* src = reinterpret_cast<const float4*>(xrow + s0);
 #pragma unroll
-      for (int i = 0; i < N / 4; ++i) {
-        const float4 t = __ldg(src + i);
-        v[4 * i] = t.x; v[4 * i + 1] = t.y; v[4 * i + 2] = t.z; v[4 * i + 3] = t.w;
-      }
-    } else {   // SciPy's zero boundary extension / end padding
-#pragma unroll
-      for (int i = 0; i < N; ++i) {
-        const long long n = s0 + i;
-        v[i] = (n >= 0 && n < a.L) ? __ldg(xrow + n) : 0.f;
-      }
+    for (int i = 0; i < N / 4; ++i) {
+      const float4 t = __ldg(src + i);
+      v[4 * i] = t.x; v[4 * i + 1] = t.y; v[4 * i + 2] = t.z; v[4 * i + 3] = t.w;
     }
-    float* Sc = S + (long long)slot * STRIDE;
-    const long long kstride = (long long)a.n_pad * STRIDE;
+  } else {   // SciPy's zero boundary extension / end padding
+#pragma unroll
+    for (int i = 0; i < N; ++i) {
+      const long long n = s0 + i;
+      v[i] = (n >= 0 && n < a.L) ? __ldg(xrow + n) : 0.f;
+    }
+  }
+}
+
+// v holds the samples of slot threadIdx.x (fetched by the caller ahead of the table set-up).
+template <int LOG2N, int STRIDE>
+__device__ __forceinline__ void fft_thread_phase(const StftArgs& a, const float* __restrict__ xrow,
+                                                 float* S, float (&v)[1 << LOG2N]) {
+  const long long kstride = (long long)a.n_pad * STRIDE;
+  if ((int)threadIdx.x < a.n_slots) {
+    float* Sc = S + (long long)threadIdx.x * STRIDE;
     frame_fft_mag<LOG2N>(v, [&](int k, float mag) { Sc[k * kstride] = log1p_pos(mag); });
+  }
+#pragma unroll 1
+  for (int slot = threadIdx.x + blockDim.x; slot < a.n_slots; slot += blockDim.x) {   // long rows only
+    float w[1 << LOG2N];
+    frame_fetch<LOG2N>(a, xrow, slot, w);
+    float* Sc = S + (long long)slot * STRIDE;
+    frame_fft_mag<LOG2N>(w, [&](int k, float mag) { Sc[k * kstride] = log1p_pos(mag); });
   }
 }
 
@@ -284,46 +296,60 @@ stft_image_kernel(const StftArgs a) {
   else if constexpr (MODE == 1) S = a.ws + (long long)blockIdx.x * a.ws_stride;
   else S = S_sm;
 
-  // Tables.  Periodic Hann scaled by 1/sum(w) = 2/N (scipy scaling='spectrum', mode 'stft').
-  if constexpr (!kThreadFft) {
-    for (int j = tid; j < N; j += nthreads)
-      win[j] = (0.5f - 0.5f * cospif(2.0f * j / N)) * (2.0f / N);
-    for (int k = tid; k < P / 2; k += nthreads)
-      tw[k] = make_float2(cospif(2.0f * k / P), -sinpif(2.0f * k / P));
-    for (int k = tid; k < P; k += nthreads)
-      utw[k] = make_float2(cospif(2.0f * k / N), sinpif(2.0f * k / N));
+  // Thread-per-frame path: the frame's samples are requested first so that their DRAM latency
+  // hides behind the table set-up; the row a later CTA will own is pulled into L2 meanwhile.
+  float v_first[kThreadFft ? N : 1];
+  if constexpr (kThreadFft) {
+    if (tid < a.n_slots) frame_fetch<LOG2N>(a, xrow, tid, v_first);
+    const long long ahead = row + (long long)(2 * 148) / a.split;
+    if (part == 0 && ahead < a.rows && (long long)tid * 32 < a.L)
+      asm volatile("prefetch.global.L2 [%0];" ::"l"(a.x + ahead * a.row_stride + (long long)tid * 32));
   }
-  if constexpr (MODE != 2) {
-    for (int f = tid; f <= F; f += nthreads) rowflag[f] = 0;
-    // First and last output column of every linear segment, as (knot slot, fraction): the
-    // extrema of a piecewise-linear row over the sampled columns can only sit there.
-    if (a.ends_only) {
-      // ends_only implies n_frames - 1 < out_cols / 2, so everything fits 32-bit integers.
-      // Segment seg covers columns [ceil(seg*D/nm1), ceil((seg+1)*D/nm1) - 1]; each thread walks a
-      // contiguous run of segments, carrying (seg*D) div/mod nm1 forward without dividing again.
-      const int nm1 = (int)a.n_frames - 1, D = a.D;
-      const int per = (nm1 + nthreads - 1) / nthreads;
-      const int seg0 = tid * per, seg1 = min(nm1, seg0 + per);
-      if (seg0 < seg1) {
-        const int dq = (int)((unsigned)D / (unsigned)nm1), dr = D - dq * nm1;
-        int q = (int)((unsigned)(seg0 * D) / (unsigned)nm1), r = seg0 * D - q * nm1;   // seg0 * D < 2^31
-        int jf = q + (r ? 1 : 0);                       // first column of seg0
-        for (int seg = seg0; seg < seg1; ++seg) {
-          q += dq; r += dr;
-          if (r >= nm1) { r -= nm1; ++q; }
-          const int jn = q + (r ? 1 : 0);               // first column of seg + 1
-          const int jl = (seg == nm1 - 1) ? D : jn - 1; // last column of seg
-          // column j sits at fraction (j*nm1 - seg*D)/D inside segment seg
-          ends[seg] = make_float2((float)(jf * nm1 - seg * D) * a.inv_d, (float)(jl * nm1 - seg * D) * a.inv_d);
-          jf = jn;
+
+  auto setup_tables = [&]() {
+  // Tables.  Periodic Hann scaled by 1/sum(w) = 2/N (scipy scaling='spectrum', mode 'stft').
+    if constexpr (!kThreadFft) {
+      for (int j = tid; j < N; j += nthreads)
+        win[j] = (0.5f - 0.5f * cospif(2.0f * j / N)) * (2.0f / N);
+      for (int k = tid; k < P / 2; k += nthreads)
+        tw[k] = make_float2(cospif(2.0f * k / P), -sinpif(2.0f * k / P));
+      for (int k = tid; k < P; k += nthreads)
+        utw[k] = make_float2(cospif(2.0f * k / N), sinpif(2.0f * k / N));
+    }
+    if constexpr (MODE != 2) {
+      for (int f = tid; f <= F; f += nthreads) rowflag[f] = 0;
+      // First and last output column of every linear segment, as (knot slot, fraction): the
+      // extrema of a piecewise-linear row over the sampled columns can only sit there.
+      if (a.ends_only) {
+        // ends_only implies n_frames - 1 < out_cols / 2, so everything fits 32-bit integers.
+        // Segment seg covers columns [ceil(seg*D/nm1), ceil((seg+1)*D/nm1) - 1]; each thread walks a
+        // contiguous run of segments, carrying (seg*D) div/mod nm1 forward without dividing again.
+        const int nm1 = (int)a.n_frames - 1, D = a.D;
+        const int per = (nm1 + nthreads - 1) / nthreads;
+        const int seg0 = tid * per, seg1 = min(nm1, seg0 + per);
+        if (seg0 < seg1) {
+          const int dq = (int)((unsigned)D / (unsigned)nm1), dr = D - dq * nm1;
+          int q = (int)((unsigned)(seg0 * D) / (unsigned)nm1), r = seg0 * D - q * nm1;   // seg0 * D < 2^31
+          int jf = q + (r ? 1 : 0);                       // first column of seg0
+          for (int seg = seg0; seg < seg1; ++seg) {
+            q += dq; r += dr;
+            if (r >= nm1) { r -= nm1; ++q; }
+            const int jn = q + (r ? 1 : 0);               // first column of seg + 1
+            const int jl = (seg == nm1 - 1) ? D : jn - 1; // last column of seg
+            // column j sits at fraction (j*nm1 - seg*D)/D inside segment seg
+            ends[seg] = make_float2((float)(jf * nm1 - seg * D) * a.inv_d, (float)(jl * nm1 - seg * D) * a.inv_d);
+            jf = jn;
+          }
         }
       }
     }
-  }
-  __syncthreads();
+  };
+  if constexpr (!kThreadFft) setup_tables();
+  if constexpr (!kThreadFft) __syncthreads();   // the thread path reads no shared table in phase 1
 
   if constexpr (kThreadFft) {
-    fft_thread_phase<LOG2N, STRIDE>(a, xrow, S);
+    fft_thread_phase<LOG2N, STRIDE>(a, xrow, S, v_first);
+    setup_tables();   // segment ends: first needed in phase 2, kept out of the FFT's register budget
     if constexpr (MODE == 2) return;
   } else {
     fft_phase<LOG2N, STRIDE>(a, xrow, S, win, tw, utw, zs);
