@@ -17,6 +17,8 @@
 //
 // HBM traffic is the algorithmic minimum: the row is read once (frames overlap in L1/L2),
 // the image is written once, nothing else touches DRAM.
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "internal.h"
 #include "stft_thread_fft.cuh"
@@ -31,6 +33,8 @@ struct StftArgs {
   int hop, half, n_slots, n_pad, gather, split, logmag_only, use_ws;
   int out_cols, D, r_step, r32_step, small_index, ends_only, n_items;
   float inv_d, eps;
+  int stage;   // thread-per-frame path: row staged in shared memory (aliases the knot array)
+  int debug;   // EEGSPEC_STFT_DEBUG (experiments): 1 = skip phases 1-2, 2 = skip phase 3
 };
 
 // Left knot and remainder of output column j:  j*(n-1) = i*D + rem, clamped to the last segment.
@@ -243,6 +247,47 @@ __device__ __forceinline__ void frame_fetch(const StftArgs& a, const float* __re
   }
 }
 
+// Row staging for the thread-per-frame path.  The zero-extended row (SciPy boundary + padding)
+// is copied into shared memory with coalesced 16-byte cp.async; every 32-sample block is padded
+// to 36 floats so that the per-thread frame reads (lane pitch = hop samples) are conflict-free
+// 128-bit loads when hop = 32.  e = sample index in the extended row (n = e - half).
+__device__ __forceinline__ int stage_index(int e) { return e + ((e >> 5) << 2); }
+
+__device__ __forceinline__ void stage_row(const StftArgs& a, const float* __restrict__ xrow, float* stage,
+                                          int n_ext) {
+  const int L = (int)a.L;
+  for (int c = threadIdx.x; 4 * c < n_ext; c += blockDim.x) {
+    const int e0 = 4 * c, n0 = e0 - a.half;
+    float* dst = stage + stage_index(e0);
+    if (n0 >= 0 && n0 + 4 <= L) {
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(dst)),
+                   "l"(xrow + n0)
+                   : "memory");
+    } else {
+      float4 z;
+      z.x = (n0 >= 0 && n0 < L) ? __ldg(xrow + n0) : 0.f;
+      z.y = (n0 + 1 >= 0 && n0 + 1 < L) ? __ldg(xrow + n0 + 1) : 0.f;
+      z.z = (n0 + 2 >= 0 && n0 + 2 < L) ? __ldg(xrow + n0 + 2) : 0.f;
+      z.w = (n0 + 3 >= 0 && n0 + 3 < L) ? __ldg(xrow + n0 + 3) : 0.f;
+      *reinterpret_cast<float4*>(dst) = z;
+    }
+  }
+  asm volatile("cp.async.commit_group;" ::: "memory");
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+}
+
+template <int LOG2N>
+__device__ __forceinline__ void frame_from_stage(const StftArgs& a, const float* stage, int slot,
+                                                 float (&v)[1 << LOG2N]) {
+  constexpr int N = 1 << LOG2N;
+  const int e0 = slot * a.hop;
+#pragma unroll
+  for (int i = 0; i < N / 4; ++i) {
+    const float4 t = *reinterpret_cast<const float4*>(stage + stage_index(e0 + 4 * i));
+    v[4 * i] = t.x; v[4 * i + 1] = t.y; v[4 * i + 2] = t.z; v[4 * i + 3] = t.w;
+  }
+}
+
 // v holds the samples of slot threadIdx.x (fetched by the caller ahead of the table set-up).
 template <int LOG2N, int STRIDE>
 __device__ __forceinline__ void fft_thread_phase(const StftArgs& a, const float* __restrict__ xrow,
@@ -284,7 +329,7 @@ stft_image_kernel(const StftArgs a) {
   int* rowflag = reinterpret_cast<int*>(win + (kThreadFft ? 0 : N));  // F + 1 (NaN rows, any)
   float* part_lo = reinterpret_cast<float*>(rowflag + F + 1 + ((F + 1) & 1));   // nthreads: partial row minima
   float* part_hi = part_lo + nthreads;                              // nthreads: partial row maxima
-  float* S_sm = part_hi + nthreads;                                 // F*n_pad*STRIDE
+  float* S_sm = reinterpret_cast<float*>((reinterpret_cast<uintptr_t>(part_hi + nthreads) + 15) & ~uintptr_t(15));  // F*n_pad*STRIDE, 16 B aligned
 
   const long long row = blockIdx.x / a.split;
   const int part = blockIdx.x % a.split;
@@ -300,9 +345,14 @@ stft_image_kernel(const StftArgs a) {
   // hides behind the table set-up; the row a later CTA will own is pulled into L2 meanwhile.
   float v_first[kThreadFft ? N : 1];
   if constexpr (kThreadFft) {
-    if (tid < a.n_slots) frame_fetch<LOG2N>(a, xrow, tid, v_first);
+    if (MODE == 0 && a.stage) {
+      stage_row(a, xrow, S_sm, (a.n_slots - 1) * a.hop + N);
+      __syncthreads();
+      if (tid < a.n_slots) frame_from_stage<LOG2N>(a, S_sm, tid, v_first);
+      __syncthreads();   // the knots are about to overwrite the staged samples
+    } else if (tid < a.n_slots && !(a.debug & 32)) frame_fetch<LOG2N>(a, xrow, tid, v_first);
     const long long ahead = row + (long long)(2 * 148) / a.split;
-    if (part == 0 && ahead < a.rows && (long long)tid * 32 < a.L)
+    if (part == 0 && ahead < a.rows && (long long)tid * 32 < a.L && !(a.debug & 64))
       asm volatile("prefetch.global.L2 [%0];" ::"l"(a.x + ahead * a.row_stride + (long long)tid * 32));
   }
 
@@ -347,6 +397,8 @@ stft_image_kernel(const StftArgs a) {
   if constexpr (!kThreadFft) setup_tables();
   if constexpr (!kThreadFft) __syncthreads();   // the thread path reads no shared table in phase 1
 
+  const long long nm1 = a.n_frames - 1;
+  if (a.debug & 1) { for (int f = tid; f <= F; f += nthreads) rowflag[f] = 0; __syncthreads(); goto phase3; }
   if constexpr (kThreadFft) {
     fft_thread_phase<LOG2N, STRIDE>(a, xrow, S, v_first);
     setup_tables();   // segment ends: first needed in phase 2, kept out of the FFT's register budget
@@ -364,7 +416,6 @@ stft_image_kernel(const StftArgs a) {
 
   // Phase 2: per-frequency min/max of the interpolated row; then every knot becomes the pair
   // {normalised value, normalised delta to the next knot} so that phase 3 is one FFMA per pixel.
-  const long long nm1 = a.n_frames - 1;
   if (a.ends_only && nthreads >= F) {
     // Up-sampling (the usual case).  Thread = (frequency row f, run of consecutive segments):
     // running min / max in two registers, lanes of a warp on consecutive rows (conflict-free:
@@ -447,6 +498,8 @@ stft_image_kernel(const StftArgs a) {
     for (int s = lane; s < a.n_slots; s += 32) Sf[s * STRIDE] = (Sf[s * STRIDE] - lo) * inv;
   }
   __syncthreads();
+phase3:
+  if (a.debug & 2) return;
 
   // Phase 3: image write.  A thread keeps the four brackets of its column quad in registers
   // and walks the frequency rows; a warp emits one contiguous 512 B line per row.
@@ -473,15 +526,34 @@ stft_image_kernel(const StftArgs a) {
     }
     float* o = orow + 4LL * q;
     const float2* Kf = reinterpret_cast<const float2*>(S);
-#pragma unroll 4
-    for (int f = 0; f < F; ++f, Kf += a.n_pad, o += a.out_cols) {
-      float v[4];
+    auto body = [&](auto UN, auto PLAIN, auto NOLDS) {
+      constexpr int kUn = decltype(UN)::value;
+#pragma unroll kUn
+      for (int f = 0; f < F; ++f, Kf += a.n_pad, o += a.out_cols) {
+        float v[4];
 #pragma unroll
-      for (int c = 0; c < 4; ++c) {
-        const float2 k = Kf[lo_i[c]];
-        v[c] = __saturatef(fmaf(k.y, fr[c], k.x));   // FFMA.SAT: [0,1] like the reference
+        for (int c = 0; c < 4; ++c) {
+          float2 k;
+          if constexpr (decltype(NOLDS)::value) k = make_float2(fr[c], fr[c]); else k = Kf[lo_i[c]];
+          v[c] = __saturatef(fmaf(k.y, fr[c], k.x));   // FFMA.SAT: [0,1] like the reference
+        }
+        if constexpr (decltype(PLAIN)::value) *reinterpret_cast<float4*>(o) = make_float4(v[0], v[1], v[2], v[3]);
+        else st_stream_f4(o, make_float4(v[0], v[1], v[2], v[3]));
       }
-      st_stream_f4(o, make_float4(v[0], v[1], v[2], v[3]));
+    };
+    using I4 = std::integral_constant<int, 4>;
+    using I11 = std::integral_constant<int, 11>;
+    using T = std::true_type;
+    using Fa = std::false_type;
+    switch ((a.debug >> 2) & 7) {
+      case 0: body(I4{}, Fa{}, Fa{}); break;
+      case 1: body(I4{}, T{}, Fa{}); break;
+      case 2: body(I11{}, Fa{}, Fa{}); break;
+      case 3: body(I11{}, T{}, Fa{}); break;
+      case 4: body(I4{}, Fa{}, T{}); break;
+      case 5: body(I4{}, T{}, T{}); break;
+      case 6: body(I11{}, Fa{}, T{}); break;
+      default: body(I11{}, T{}, T{}); break;
     }
   }
   // Rows poisoned by a NaN sample: torch.min/max propagate NaN, the whole row is NaN.  The
@@ -510,6 +582,7 @@ static size_t stft_fixed_smem(int nperseg, int threads, long long n_ends) {
   b += sizeof(float2) * n_ends;
   b += sizeof(int) * (F + 1 + ((F + 1) & 1));
   b += sizeof(float) * 2 * threads;   // partial row minima / maxima
+  b += 16;                            // the knot array starts 16-byte aligned
   return b;
 }
 
@@ -673,6 +746,16 @@ int stft_image_launch(const float* x, long long rows, long long length, long lon
   a.split = s.split;
   a.logmag_only = 0;
   a.use_ws = s.use_ws;
+  {
+    // Row staging (thread-per-frame path): one pass over the slots, 16-byte alignment everywhere,
+    // and the padded extended row has to fit the knot array it aliases.
+    const long long n_ext = (pl.n_slots - 1) * (long long)pl.hop + nperseg;
+    const long long stage_floats = n_ext + ((n_ext >> 5) << 2) + 8;
+    a.stage = (nperseg <= 64 && !s.use_ws && !pl.gather && pl.n_slots <= s.threads && (pl.hop & 3) == 0 &&
+               (pl.half & 3) == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0 && (row_stride & 3) == 0 &&
+               length < (1LL << 30) &&
+               stage_floats * sizeof(float) <= sizeof(float2) * (size_t)pl.n_freqs * s.n_pad) ? 1 : 0;
+  }
   a.out_cols = (int)out_cols;
   a.D = (int)out_cols - 1;
   a.q_step = (pl.n_frames - 1) / a.D;
@@ -684,6 +767,7 @@ int stft_image_launch(const float* x, long long rows, long long length, long lon
   a.small_index = ((double)out_cols * (double)pl.n_frames < 4.0e9) ? 1 : 0;
   a.inv_d = 1.0f / (float)a.D;
   a.eps = eps;
+  { static const int dbg = [] { const char* v = getenv("EEGSPEC_STFT_DEBUG"); return v ? atoi(v) : 0; }(); a.debug = dbg; }
   return dispatch(nperseg, a, s.grid, s.smem, s.threads, st);
 }
 
