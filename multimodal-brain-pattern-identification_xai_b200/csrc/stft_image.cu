@@ -17,8 +17,6 @@
 //
 // HBM traffic is the algorithmic minimum: the row is read once (frames overlap in L1/L2),
 // the image is written once, nothing else touches DRAM.
-#include <stdlib.h>
-
 #include "common.cuh"
 #include "internal.h"
 #include "stft_thread_fft.cuh"
@@ -34,7 +32,6 @@ struct StftArgs {
   int out_cols, D, r_step, r32_step, small_index, ends_only, n_items;
   float inv_d, eps;
   int stage;   // thread-per-frame path: row staged in shared memory (aliases the knot array)
-  int debug;   // EEGSPEC_STFT_DEBUG (experiments): 1 = skip phases 1-2, 2 = skip phase 3
 };
 
 // Left knot and remainder of output column j:  j*(n-1) = i*D + rem, clamped to the last segment.
@@ -350,9 +347,9 @@ stft_image_kernel(const StftArgs a) {
       __syncthreads();
       if (tid < a.n_slots) frame_from_stage<LOG2N>(a, S_sm, tid, v_first);
       __syncthreads();   // the knots are about to overwrite the staged samples
-    } else if (tid < a.n_slots && !(a.debug & 32)) frame_fetch<LOG2N>(a, xrow, tid, v_first);
+    } else if (tid < a.n_slots) frame_fetch<LOG2N>(a, xrow, tid, v_first);
     const long long ahead = row + (long long)(2 * 148) / a.split;
-    if (part == 0 && ahead < a.rows && (long long)tid * 32 < a.L && !(a.debug & 64))
+    if (part == 0 && ahead < a.rows && (long long)tid * 32 < a.L)
       asm volatile("prefetch.global.L2 [%0];" ::"l"(a.x + ahead * a.row_stride + (long long)tid * 32));
   }
 
@@ -398,7 +395,6 @@ stft_image_kernel(const StftArgs a) {
   if constexpr (!kThreadFft) __syncthreads();   // the thread path reads no shared table in phase 1
 
   const long long nm1 = a.n_frames - 1;
-  if (a.debug & 1) { for (int f = tid; f <= F; f += nthreads) rowflag[f] = 0; __syncthreads(); goto phase3; }
   if constexpr (kThreadFft) {
     fft_thread_phase<LOG2N, STRIDE>(a, xrow, S, v_first);
     setup_tables();   // segment ends: first needed in phase 2, kept out of the FFT's register budget
@@ -498,8 +494,6 @@ stft_image_kernel(const StftArgs a) {
     for (int s = lane; s < a.n_slots; s += 32) Sf[s * STRIDE] = (Sf[s * STRIDE] - lo) * inv;
   }
   __syncthreads();
-phase3:
-  if (a.debug & 2) return;
 
   // Phase 3: image write.  A thread keeps the four brackets of its column quad in registers
   // and walks the frequency rows; a warp emits one contiguous 512 B line per row.
@@ -526,34 +520,15 @@ phase3:
     }
     float* o = orow + 4LL * q;
     const float2* Kf = reinterpret_cast<const float2*>(S);
-    auto body = [&](auto UN, auto PLAIN, auto NOLDS) {
-      constexpr int kUn = decltype(UN)::value;
-#pragma unroll kUn
-      for (int f = 0; f < F; ++f, Kf += a.n_pad, o += a.out_cols) {
-        float v[4];
+#pragma unroll 4
+    for (int f = 0; f < F; ++f, Kf += a.n_pad, o += a.out_cols) {
+      float v[4];
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
-          float2 k;
-          if constexpr (decltype(NOLDS)::value) k = make_float2(fr[c], fr[c]); else k = Kf[lo_i[c]];
-          v[c] = __saturatef(fmaf(k.y, fr[c], k.x));   // FFMA.SAT: [0,1] like the reference
-        }
-        if constexpr (decltype(PLAIN)::value) *reinterpret_cast<float4*>(o) = make_float4(v[0], v[1], v[2], v[3]);
-        else st_stream_f4(o, make_float4(v[0], v[1], v[2], v[3]));
+      for (int c = 0; c < 4; ++c) {
+        const float2 k = Kf[lo_i[c]];
+        v[c] = __saturatef(fmaf(k.y, fr[c], k.x));   // FFMA.SAT: [0,1] like the reference
       }
-    };
-    using I4 = std::integral_constant<int, 4>;
-    using I11 = std::integral_constant<int, 11>;
-    using T = std::true_type;
-    using Fa = std::false_type;
-    switch ((a.debug >> 2) & 7) {
-      case 0: body(I4{}, Fa{}, Fa{}); break;
-      case 1: body(I4{}, T{}, Fa{}); break;
-      case 2: body(I11{}, Fa{}, Fa{}); break;
-      case 3: body(I11{}, T{}, Fa{}); break;
-      case 4: body(I4{}, Fa{}, T{}); break;
-      case 5: body(I4{}, T{}, T{}); break;
-      case 6: body(I11{}, Fa{}, T{}); break;
-      default: body(I11{}, T{}, T{}); break;
+      st_stream_f4(o, make_float4(v[0], v[1], v[2], v[3]));
     }
   }
   // Rows poisoned by a NaN sample: torch.min/max propagate NaN, the whole row is NaN.  The
@@ -767,7 +742,6 @@ int stft_image_launch(const float* x, long long rows, long long length, long lon
   a.small_index = ((double)out_cols * (double)pl.n_frames < 4.0e9) ? 1 : 0;
   a.inv_d = 1.0f / (float)a.D;
   a.eps = eps;
-  { static const int dbg = [] { const char* v = getenv("EEGSPEC_STFT_DEBUG"); return v ? atoi(v) : 0; }(); a.debug = dbg; }
   return dispatch(nperseg, a, s.grid, s.smem, s.threads, st);
 }
 
