@@ -160,6 +160,27 @@ __device__ __forceinline__ void c_tmem_ld8x2(uint32_t addr_re, uint32_t addr_im,
 #pragma unroll
   for (int i = 0; i < 8; ++i) { re[i] = __uint_as_float(a[i]); im[i] = __uint_as_float(b[i]); }
 }
+// 8 TMEM columns of this thread's lane: store (issue only) / load + wait.
+__device__ __forceinline__ void c_tmem_st8(uint32_t addr, float v0, float v1, float v2, float v3, float v4, float v5,
+                                           float v6, float v7) {
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};\n" ::"r"(addr),
+               "r"(__float_as_uint(v0)), "r"(__float_as_uint(v1)), "r"(__float_as_uint(v2)), "r"(__float_as_uint(v3)),
+               "r"(__float_as_uint(v4)), "r"(__float_as_uint(v5)), "r"(__float_as_uint(v6)), "r"(__float_as_uint(v7))
+               : "memory");
+}
+__device__ __forceinline__ void c_tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;\n" ::: "memory"); }
+__device__ __forceinline__ void c_tmem_ld8(uint32_t addr, float (&v)[8]) {
+  uint32_t a[8];
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];\n"
+               : "=r"(a[0]), "=r"(a[1]), "=r"(a[2]), "=r"(a[3]), "=r"(a[4]), "=r"(a[5]), "=r"(a[6]), "=r"(a[7])
+               : "r"(addr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;\n"
+               : "+r"(a[0]), "+r"(a[1]), "+r"(a[2]), "+r"(a[3]), "+r"(a[4]), "+r"(a[5]), "+r"(a[6]), "+r"(a[7])
+               :
+               : "memory");
+#pragma unroll
+  for (int i = 0; i < 8; ++i) v[i] = __uint_as_float(a[i]);
+}
 // x = hi + lo with hi the 11-bit truncation of x (exact in fp16 for the pre-scaled range).
 __device__ __forceinline__ void c_split2(float x0, float x1, uint32_t& hi, uint32_t& lo) {
   const float h0 = __uint_as_float(__float_as_uint(x0) & 0xFFFFE000u);

@@ -7,17 +7,25 @@
 // deferred fold of the pair maximum exchanged through distributed shared memory), but instead
 // of 16 warps walking build -> epilogue -> difference in lockstep:
 //
-//   warps  0- 7  epilogue   thread = (frame, 64 mels): tcgen05.ld, power, mel taps, lg2, fold;
-//                           keeps acc[64] / qprev[64] in registers (setmaxnreg.inc)
-//   warps  8-15  build      electrode difference, NaN statistics, max|y|, fp16 hi/lo operand
+//   4 NQ warps   epilogue   thread = (frame, 128/NQ mels): tcgen05.ld, power, mel taps, lg2, sum;
+//                           keeps the chain sum acc[] in registers (setmaxnreg.inc)
+//   8 warps      build      electrode difference, NaN statistics, max|y|, fp16 hi/lo operand
 //                           tiles of the next pair -- LSU / conversion work that overlaps the
 //                           epilogue group's FMA / MUFU work on the previous pair
-//   warp  16     mma        one lane issues the tcgen05.mma stream of a tile and its commit
-//   warp  17     loader     one lane issues the cp.async.bulk (TMA) prefetch of the electrode rows
-//   warp  18     publisher  one lane reduces the per-warp maxima of a finished tile and exchanges
+//   1 warp       mma        one lane issues the tcgen05.mma stream of a tile and its commit
+//   1 warp       loader     one lane issues the cp.async.bulk (TMA) prefetch of the electrode rows
+//   1 warp       publisher  one lane reduces the per-warp maxima of a finished tile and exchanges
 //                           them with the peer CTA (st.shared::cluster + remote mbarrier arrive)
 //
 // All hand-offs are mbarriers; the only CTA-scope barriers are named barriers inside one group.
+//
+// Deferred fold without register cost.  power_to_db clips every pair image at max - top_db (and
+// at amin); the clip level is only known once both halves of the pair have been reduced and
+// exchanged, one tile later.  The lockstep kernel carries the pair's log values in registers
+// until then (and spills); here a thread parks them in tensor memory instead: it writes its
+// log-mel values over accumulator columns that only it has read (tcgen05.st), and the next
+// tile's epilogue reads them back (tcgen05.ld), folds them with the now known clip level into
+// the chain sum and only then hands the accumulator buffer back to the MMA warp.
 //
 // Front half follows the reference (pair list /root/reference/root/config/config.yml:529-545,
 // differencing /root/reference/root/src/utils/data_utils.py:183-215, crop
@@ -29,18 +37,16 @@
 
 namespace eegspec {
 
-constexpr int kREpiWarps = 8, kRBuildWarps = 8;
-constexpr int kREpi = 32 * kREpiWarps, kRBuild = 32 * kRBuildWarps;
-constexpr int kRThreads = kREpi + kRBuild + 128;   // + one warp group of single-lane roles
-constexpr int kRMmaWarp = kREpiWarps + kRBuildWarps, kRLoadWarp = kRMmaWarp + 1, kRPubWarp = kRMmaWarp + 2;
+constexpr int kRBuildWarps = 8, kRBuild = 32 * kRBuildWarps;
+constexpr int kRMaxEpiWarps = 16;
 constexpr int kRYFloats = kCStageFloats + 2 * kCMargin + 128;
 
 struct RolesShared {
-  unsigned long long load_bar, stage_free, ops_bar, mma_bar[2], tmem_free[2], xch_bar[2];
+  unsigned long long load_bar, stage_free, ops_bar, mma_bar[2], tmem_free[2], epi_done[2], xch_bar[2];
   uint32_t tmem_base;
   int e_tile[4];                    // power-of-two pre-scale exponent of tile j, [j & 3]
   float w_amax[kRBuildWarps];       // per-warp max|y| of the pair being differenced (NaN if any NaN)
-  float w_vmax[2][kREpiWarps];      // per-warp log2 mel maximum of tile j (unscaled units), [j & 1]
+  float w_vmax[2][kRMaxEpiWarps];      // per-warp log2 mel maximum of tile j (unscaled units), [j & 1]
   float xch[2][2];                  // [exchange & 1][cluster rank]: log2 of the pair maximum
   float red[kRBuildWarps];
   float px[kCMaxExtra * 128];       // power spectrum of the extra frames [frame][bin slot]
@@ -48,8 +54,11 @@ struct RolesShared {
   float mel_w0[kMaxMels], mel_w1[kMaxMels];
 };
 
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kRThreads, 1)
+template <int NQ>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(128 * NQ + kRBuild + 128, 1)
 melspec_roles_kernel(const ChainArgs a) {
+  constexpr int kREpiWarps = 4 * NQ, kREpi = 128 * NQ, kMels = 128 / NQ;
+  constexpr int kRMmaWarp = kREpiWarps + kRBuildWarps, kRLoadWarp = kRMmaWarp + 1, kRPubWarp = kRMmaWarp + 2;
   extern __shared__ __align__(128) unsigned char smem_raw[];
   unsigned char* tab = smem_raw;                                       // Ch | Cl | Sh | Sl
   unsigned char* tiles = tab + 4 * kCTabBytes;                         // Eh | El | Oh | Ol
@@ -69,7 +78,7 @@ melspec_roles_kernel(const ChainArgs a) {
   const uint32_t load_bar = c_smem_u32(&sh.load_bar), stage_free = c_smem_u32(&sh.stage_free);
   const uint32_t ops_bar = c_smem_u32(&sh.ops_bar);
   const uint32_t mma_bar0 = c_smem_u32(&sh.mma_bar[0]), tmem_free0 = c_smem_u32(&sh.tmem_free[0]);
-  const uint32_t xch_bar0 = c_smem_u32(&sh.xch_bar[0]);
+  const uint32_t xch_bar0 = c_smem_u32(&sh.xch_bar[0]), epi_done0 = c_smem_u32(&sh.epi_done[0]);
   if (warp == 0) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(c_smem_u32(&sh.tmem_base)), "r"(512));
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
@@ -81,6 +90,7 @@ melspec_roles_kernel(const ChainArgs a) {
     for (int b = 0; b < 2; ++b) {
       c_mbar_init(mma_bar0 + 8 * b, 1);
       c_mbar_init(tmem_free0 + 8 * b, kREpiWarps);
+      c_mbar_init(epi_done0 + 8 * b, kREpiWarps);
       c_mbar_init(xch_bar0 + 8 * b, 2);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::);
@@ -121,10 +131,10 @@ melspec_roles_kernel(const ChainArgs a) {
   // The register file is partitioned per scheduler: this warp group gives its registers back so
   // that the epilogue group can hold its accumulators (setmaxnreg).
   if (warp >= kRMmaWarp) {
-    asm volatile("setmaxnreg.dec.sync.aligned.u32 24;");
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
     if (warp == kRMmaWarp) {
       // ---- the tcgen05.mma stream: tile j as soon as its operands are built and the
-      //      accumulator buffer (j & 1) has been drained by the epilogue of tile j - 2
+      //      accumulator buffer (j & 1) has been handed back (tile j - 2 folded, during epilogue j - 1)
       for (int j = 0; j < J; ++j) {
         c_mbar_wait(ops_bar, j & 1);
         if (j >= 2) c_mbar_wait(tmem_free0 + 8 * (j & 1), ((j - 2) >> 1) & 1);
@@ -183,7 +193,7 @@ melspec_roles_kernel(const ChainArgs a) {
       // ---- publish the maximum of every finished tile to both CTAs of the cluster
       if (lane == 0) {
         for (int j = 0; j < J; ++j) {
-          c_mbar_wait(tmem_free0 + 8 * (j & 1), (j >> 1) & 1);
+          c_mbar_wait(epi_done0 + 8 * (j & 1), (j >> 1) & 1);
           float r_true = sh.w_vmax[j & 1][0];   // per-warp log2 maxima, already in unscaled units
           for (int w = 1; w < kREpiWarps; ++w) r_true = fmaxf(r_true, sh.w_vmax[j & 1][w]);
           float* slot = &sh.xch[j & 1][h];
@@ -338,56 +348,78 @@ melspec_roles_kernel(const ChainArgs a) {
     }
   } else {
     // ============================================================================= epilogue group
-    // thread = (frame t = TMEM lane, part q): owns mels [64 q, 64 q + 64) of frame 128 h + t and
-    // keeps the chain sum acc[] and the previous pair's log-mel values qprev[] in registers.
-    asm volatile("setmaxnreg.inc.sync.aligned.u32 168;");
-    constexpr int kMels = 64;
+    // thread = (frame t = TMEM lane, part q): owns mels [q, q + 1) * 128 / NQ of frame 128 h + t
+    // and keeps their chain sum acc[] in registers; the log-mel values of the tile in flight are
+    // parked in accumulator columns only this thread reads (bins exclusive to its part).
+    if constexpr (NQ == 4) asm volatile("setmaxnreg.inc.sync.aligned.u32 88;");    // launch: 72 x 896
+    else asm volatile("setmaxnreg.inc.sync.aligned.u32 160;");                     // launch: 96 x 640
     const int t_frame = tid & (kTileFrames - 1), part = tid >> 7;
-    float acc[kMels], qprev[kMels];
+    // Parking columns of log-value group g (8 mels): the part's load chunk 1 + g / 2, Re half for
+    // even g, Im half for odd g.  Those bins are read by this part only, and the generated
+    // epilogue has consumed the chunk by the time the group is stored (one group late).
+    const uint32_t qcol = NQ == 4 ? (uint32_t)(MELGEN_COL0_P4_1 * part) : (uint32_t)(MELGEN_COL0_P2_1 * part);
+    static_assert(MELGEN_COL0_P4_2 == 2 * MELGEN_COL0_P4_1 && MELGEN_COL0_P4_3 == 3 * MELGEN_COL0_P4_1, "part pitch");
+    auto park_col = [](int g) { return (uint32_t)(8 * (1 + g / 2) + (g & 1) * kCBins); };
+    const uint32_t lane_base = tmem_base + ((uint32_t)(32 * (warp & 3)) << 16);
+    float acc[kMels];
 #pragma unroll
-    for (int i = 0; i < kMels; ++i) { acc[i] = 0.f; qprev[i] = 0.f; }
-    float csum = 0.f;
+    for (int i = 0; i < kMels; ++i) acc[i] = 0.f;
+    float csum = 0.f;   // sum over the item's pairs of (reference + 2 e)
     int e_prev = 0;
 
-    auto flush = [&](int j_last, float t_fold) {   // write the item whose last tile is j_last
+    // exchange n is complete: fold the parked log values of tile n into the chain sum with the
+    // pair's clip level, then hand accumulator buffer n & 1 back to the MMA warp.
+    auto fold_tile = [&](int n) {
+      c_mbar_wait_cluster(xch_bar0 + 8 * (n & 1), (uint32_t)((n >> 1) & 1));
+      const float r_pair = fmaxf(fmaxf(sh.xch[n & 1][0], sh.xch[n & 1][1]), a.log2_amin);
+      const float off = 2.f * (float)e_prev;          // e_prev = pre-scale exponent of tile n
+      const float t_clip = fmaxf(a.log2_amin, r_pair - a.top_log2) + off;
+      csum += r_pair + off;
+      const uint32_t qaddr = lane_base + (n & 1) * kCAccCols + qcol;
+#pragma unroll
+      for (int g = 0; g < kMels / 8; ++g) {
+        float q[8];
+        c_tmem_ld8(qaddr + park_col(g), q);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) acc[8 * g + i] += fmaxf(q[i], t_clip);
+      }
+      asm volatile("tcgen05.fence::before_thread_sync;" ::);
+      __syncwarp();
+      if (lane == 0) c_mbar_arrive(tmem_free0 + 8 * (n & 1));
+    };
+    auto flush = [&](int j_last) {   // write the item whose last tile is j_last
       int rec, chain;
       pair_of(j_last, rec, chain);
       float* o = a.out + (((long long)rec * a.n_mels + kMels * part) * a.n_time + 128 * h + t_frame) * a.n_chains + chain;
       const int mstride = a.n_time * a.n_chains;
 #pragma unroll
-      for (int i = 0; i < kMels; ++i)
-        o[i * mstride] = fmaf(a.out_gain, acc[i] + fmaxf(qprev[i], t_fold) - csum, a.out_bias);
-    };
-    auto fold_constants = [&](int n, float& t_out) {   // exchange n: threshold and reference of tile n
-      c_mbar_wait_cluster(xch_bar0 + 8 * (n & 1), (uint32_t)((n >> 1) & 1));
-      const float r_pair = fmaxf(fmaxf(sh.xch[n & 1][0], sh.xch[n & 1][1]), a.log2_amin);
-      const float off = 2.f * (float)e_prev;          // e_prev = pre-scale exponent of tile n
-      t_out = fmaxf(a.log2_amin, r_pair - a.top_log2) + off;
-      csum += r_pair + off;
+      for (int i = 0; i < kMels; ++i) o[i * mstride] = fmaf(a.out_gain, acc[i] - csum, a.out_bias);
     };
 
     for (int j = 0; j < J; ++j) {
       c_mbar_wait(mma_bar0 + 8 * (j & 1), (j >> 1) & 1);
       asm volatile("tcgen05.fence::after_thread_sync;" ::);
       const int e_j = sh.e_tile[j & 3];
-      float t_prev = 0.f;   // clip threshold of tile j-1, in that tile's scaled log2 units
-      if (j >= 1) fold_constants(j - 1, t_prev);
-      float t_fold = t_prev;
+      if (j >= 1) fold_tile(j - 1);
       if (j % a.ppc == 0) {   // first pair of an item: write the finished one, start afresh
-        if (j > 0) flush(j - 1, t_prev);
+        if (j > 0) flush(j - 1);
 #pragma unroll
-        for (int i = 0; i < kMels; ++i) { acc[i] = 0.f; qprev[i] = 0.f; }
+        for (int i = 0; i < kMels; ++i) acc[i] = 0.f;
         csum = 0.f;
-        t_fold = 0.f;
       }
-      const uint32_t lane_addr = tmem_base + ((uint32_t)(32 * (warp & 3)) << 16) + (j & 1) * kCAccCols;
+      const uint32_t lane_addr = lane_base + (j & 1) * kCAccCols;
+      const uint32_t qaddr = lane_addr + qcol;
       float vmax = 0.f;
-      float re[8], im[8];
+      float re[8], im[8], qb[16];
 #define CH_POW(s, i) const float p##s = fmaf(re[i], re[i], im[i] * im[i]);
-#define CH_MEL_TAIL(i)                       \
-  vmax = fmaxf(vmax, v);                     \
-  acc[i] += fmaxf(qprev[i], t_fold);         \
-  qprev[i] = c_lg2(v);
+#define CH_MEL_TAIL(i)                                                                                   \
+  vmax = fmaxf(vmax, v);                                                                                 \
+  qb[(i) & 15] = c_lg2(v);                                                                               \
+  if (((i) & 7) == 7 && (i) >= 15) CH_PARK(((i) - 15) / 8)
+#define CH_PARK(g)                                                                                               \
+  c_tmem_st8(qaddr + park_col(g), qb[(8 * (g)) & 15], qb[(8 * (g) + 1) & 15], qb[(8 * (g) + 2) & 15],             \
+             qb[(8 * (g) + 3) & 15], qb[(8 * (g) + 4) & 15], qb[(8 * (g) + 5) & 15], qb[(8 * (g) + 6) & 15],      \
+             qb[(8 * (g) + 7) & 15]);
 #define CH_MEL1(i, sa, w0) { const float v = (w0) * p##sa; CH_MEL_TAIL(i) }
 #define CH_MEL2(i, sa, sb, w0, w1) { const float v = fmaf(w1, p##sb, (w0) * p##sa); CH_MEL_TAIL(i) }
 #define CH_LOAD(c) c_tmem_ld8x2(lane_addr + col0 + 8 * (c), lane_addr + kCBins + col0 + 8 * (c), re, im);
@@ -396,11 +428,18 @@ melspec_roles_kernel(const ChainArgs a) {
     constexpr int col0 = MELGEN_COL0_##TAG;                         \
     MELGEN_EPILOGUE_##TAG(CH_LOAD, CH_POW, CH_MEL1, CH_MEL2)        \
   }
-      if (part == 0) CH_PART(P2_0) else CH_PART(P2_1)
+      if constexpr (NQ == 2) {
+        if (part == 0) CH_PART(P2_0) else CH_PART(P2_1)
+      } else {
+        if (part == 0) CH_PART(P4_0) else if (part == 1) CH_PART(P4_1) else if (part == 2) CH_PART(P4_2) else CH_PART(P4_3)
+      }
+      CH_PARK(kMels / 8 - 1)
+      c_tmem_wait_st();
 #undef CH_PART
 #undef CH_LOAD
 #undef CH_POW
 #undef CH_MEL_TAIL
+#undef CH_PARK
 #undef CH_MEL1
 #undef CH_MEL2
 
@@ -422,16 +461,14 @@ melspec_roles_kernel(const ChainArgs a) {
       }
       vmax = warp_max_nan(vmax);
       if (lane == 0) sh.w_vmax[j & 1][warp] = c_lg2(vmax) - 2.f * (float)e_j;
-      asm volatile("tcgen05.fence::before_thread_sync;" ::);
       __syncwarp();
-      if (lane == 0) c_mbar_arrive(tmem_free0 + 8 * (j & 1));
+      if (lane == 0) c_mbar_arrive(epi_done0 + 8 * (j & 1));   // the publisher may exchange the maximum of tile j
       e_prev = e_j;
     }
 
-    // ---- the last pair's maximum has been exchanged: write the last item
-    float t_last;
-    fold_constants(J - 1, t_last);
-    flush(J - 1, t_last);
+    // ---- the last pair's maximum has been exchanged: fold it and write the last item
+    fold_tile(J - 1);
+    flush(J - 1);
   }
 
   asm volatile("tcgen05.fence::before_thread_sync;" ::);
@@ -448,7 +485,8 @@ size_t melspec_roles_smem_bytes() {
 }
 
 // Launches the role-split kernel on `clusters` clusters of two CTAs (arguments prepared by
-// melspec_chain_launch, which owns the geometry checks).
+// melspec_chain_launch, which owns the geometry checks).  EEGSPEC_ROLES_NQ = 2 | 4 picks the
+// number of mel parts per frame (8 or 16 epilogue warps); 4 is the default.
 int melspec_roles_run(const ChainArgs& a, long long clusters, cudaStream_t st) {
   static bool configured[64] = {};
   int dev = 0;
@@ -456,11 +494,15 @@ int melspec_roles_run(const ChainArgs& a, long long clusters, cudaStream_t st) {
   if (dev < 0 || dev >= 64) return EEGSPEC_EUNSUPPORTED;
   const size_t smem = melspec_roles_smem_bytes();
   if (!configured[dev]) {
-    cudaError_t e = cudaFuncSetAttribute(melspec_roles_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = cudaFuncSetAttribute(melspec_roles_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return (int)e;
+    e = cudaFuncSetAttribute(melspec_roles_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return (int)e;
     configured[dev] = true;
   }
-  melspec_roles_kernel<<<(unsigned)(2 * clusters), kRThreads, smem, st>>>(a);
+  static const int nq = [] { const char* v = getenv("EEGSPEC_ROLES_NQ"); return (v && v[0] == '2') ? 2 : 4; }();
+  if (nq == 2) melspec_roles_kernel<2><<<(unsigned)(2 * clusters), 128 * 2 + kRBuild + 128, smem, st>>>(a);
+  else melspec_roles_kernel<4><<<(unsigned)(2 * clusters), 128 * 4 + kRBuild + 128, smem, st>>>(a);
   return (int)cudaGetLastError();
 }
 
