@@ -460,6 +460,9 @@ int melspec_chain_launch(const MelArgs& m, const eegspec_mel_params& p, long lon
   if ((reinterpret_cast<uintptr_t>(m.eeg) & 15) || (m.rec_stride & 3) || (m.ch_stride & 3) || (m.crop_off & 3))
     return EEGSPEC_EUNSUPPORTED;
   ChainArgs a;
+  a.tl = nullptr;
+  a.tl_j0 = 0;
+  a.stagger_ns = 0;
   a.eeg = m.eeg;
   a.out = m.out;
   a.tab = m.t.tc3_tab;
@@ -516,6 +519,22 @@ int melspec_chain_launch(const MelArgs& m, const eegspec_mel_params& p, long lon
   // EEGSPEC_CHAIN_NQ = 2 | 4 selects the lockstep kernel of this file (2 or 4 mel parts per frame);
   // the default is the role-split kernel (melspec_roles.cu).
   static const int nq = [] { const char* v = getenv("EEGSPEC_CHAIN_NQ"); return v ? (v[0] == '2' ? 2 : 4) : 0; }();
+  // EEGSPEC_ENGINE3 = roles forces the older role-split kernel (operands in shared memory).
+  static const bool force_roles = [] { const char* v = getenv("EEGSPEC_ENGINE3"); return v && v[0] == 'r'; }();
+  if (nq == 0 && !force_roles && a.n_chains == 4 && a.ppc == 4 && a.n_mels == 128) {
+    // default: operands in tensor memory, work item = record (melspec_ts.cu)
+    ChainArgs b = a;
+    b.n_items = batch;
+    static const unsigned stagger = [] { const char* v = getenv("EEGSPEC_STAGGER_NS"); return v ? (unsigned)atoi(v) : 2500u; }();
+    b.stagger_ns = stagger;
+    long long cl = sm_count[dev] / 2;
+    if (cl < 1) cl = 1;
+    if (cl > batch) cl = batch;
+    if ((batch + cl - 1) / cl * 16 > (1LL << 28)) return EEGSPEC_EUNSUPPORTED;
+    const int rc = melspec_ts_run(b, cl, st);
+    if (rc == 0) count_launch();
+    return rc;
+  }
   if (nq == 0) {
     const int rc = melspec_roles_run(a, clusters, st);
     if (rc == 0) count_launch();

@@ -34,6 +34,9 @@ struct ChainArgs {
   int seg_lo[2], seg_n[2];     // staged sample range of each half (multiples of 4)
   float log2_amin, top_log2, out_bias, out_gain;
   int pair_a[EEGSPEC_MAX_PAIRS], pair_b[EEGSPEC_MAX_PAIRS];
+  long long* tl;               // debug timeline (EEGSPEC_TIMELINE), normally null
+  int tl_j0;
+  unsigned int stagger_ns;     // melspec_ts.cu: start delay per quarter-chain of stagger
 };
 
 // ------------------------------------------------------------------------------ PTX helpers
@@ -77,14 +80,17 @@ __device__ __forceinline__ void c_tmem_ld4(uint32_t addr, float (&v)[4]) {
 __device__ __forceinline__ void c_mbar_init(uint32_t bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
 }
+// The suspend-time hint lets the hardware park the waiting warp until the phase completes instead
+// of spinning: spinning waiters steal issue slots from the single-lane MMA / loader warps that
+// share their scheduler (measured: 6 MMAs took 800-1400 cycles to ISSUE next to hot spin loops).
 __device__ __forceinline__ void c_mbar_wait(uint32_t bar, uint32_t parity) {
   asm volatile(
       "{\n\t.reg .pred P1;\n\t"
       "CW_%=:\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1, %2;\n\t"
       "@!P1 bra CW_%=;\n\t}\n"
       :
-      : "r"(bar), "r"(parity)
+      : "r"(bar), "r"(parity), "r"(0x989680u)
       : "memory");
 }
 __device__ __forceinline__ void c_mbar_expect_tx(uint32_t bar, uint32_t bytes) {
@@ -216,5 +222,7 @@ __device__ __forceinline__ void c_named_bar(int id, int threads) {
 
 // melspec_roles.cu: the role-split variant of the engine-3 kernel (the default).
 int melspec_roles_run(const ChainArgs& a, long long clusters, cudaStream_t st);
+// melspec_ts.cu: frame operand in tensor memory, work item = record (a.n_items = records).
+int melspec_ts_run(const ChainArgs& a, long long clusters, cudaStream_t st);
 
 }  // namespace eegspec

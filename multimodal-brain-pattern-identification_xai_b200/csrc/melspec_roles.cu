@@ -30,7 +30,10 @@
 // Front half follows the reference (pair list /root/reference/root/config/config.yml:529-545,
 // differencing /root/reference/root/src/utils/data_utils.py:183-215, crop
 // /root/reference/root/src/utils/cfg_utils.py:369-371, NaN fill cfg_utils.py:380-385).
+#include <stdio.h>
 #include <stdlib.h>
+
+#include <vector>
 
 #include "mel_default_epilogue.h"
 #include "melspec_chain.cuh"
@@ -39,6 +42,7 @@ namespace eegspec {
 
 constexpr int kRBuildWarps = 8, kRBuild = 32 * kRBuildWarps;
 constexpr int kRMaxEpiWarps = 16;
+constexpr int kTlTiles = 64, kTlSlots = 32;
 constexpr int kRYFloats = kCStageFloats + 2 * kCMargin + 128;
 
 struct RolesShared {
@@ -71,6 +75,8 @@ melspec_roles_kernel(const ChainArgs a) {
   const int h = (int)c_cluster_rank(), peer = h ^ 1;
   const int cluster_id = blockIdx.x >> 1, n_clusters = gridDim.x >> 1;
   const int n_items = (int)a.n_items;
+  // debug timeline: clock stamps of the first kTlTiles tiles of CTAs 0 and 1 (a.tl is normally null)
+#define TL(slot) do { if (a.tl != nullptr && blockIdx.x < 2 && lane == 0 && j >= a.tl_j0 && j < a.tl_j0 + kTlTiles) a.tl[((blockIdx.x * kTlTiles + (j - a.tl_j0)) * kTlSlots) + (slot)] = clock64(); } while (0)
   const int n_my_items = n_items > cluster_id ? (n_items - cluster_id + n_clusters - 1) / n_clusters : 0;
   const int J = n_my_items * a.ppc;
   if (J == 0) return;   // both CTAs of the cluster agree
@@ -137,7 +143,9 @@ melspec_roles_kernel(const ChainArgs a) {
       //      accumulator buffer (j & 1) has been handed back (tile j - 2 folded, during epilogue j - 1)
       for (int j = 0; j < J; ++j) {
         c_mbar_wait(ops_bar, j & 1);
+        TL(5);
         if (j >= 2) c_mbar_wait(tmem_free0 + 8 * (j & 1), ((j - 2) >> 1) & 1);
+        TL(6);
         asm volatile("tcgen05.fence::after_thread_sync;" ::);
         if (lane == 0) {
           const uint32_t tab0 = c_smem_u32(tab), til0 = c_smem_u32(tiles), xt0 = c_smem_u32(xt);
@@ -167,6 +175,7 @@ melspec_roles_kernel(const ChainArgs a) {
           asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(mma_bar0 + 8 * (j & 1))
                        : "memory");
         }
+        TL(7);
         __syncwarp();
       }
     } else if (warp == kRLoadWarp) {
@@ -194,6 +203,7 @@ melspec_roles_kernel(const ChainArgs a) {
       if (lane == 0) {
         for (int j = 0; j < J; ++j) {
           c_mbar_wait(epi_done0 + 8 * (j & 1), (j >> 1) & 1);
+          TL(14);
           float r_true = sh.w_vmax[j & 1][0];   // per-warp log2 maxima, already in unscaled units
           for (int w = 1; w < kREpiWarps; ++w) r_true = fmaxf(r_true, sh.w_vmax[j & 1][w]);
           float* slot = &sh.xch[j & 1][h];
@@ -202,6 +212,7 @@ melspec_roles_kernel(const ChainArgs a) {
           const uint32_t xb = xch_bar0 + 8 * (j & 1);
           c_mbar_arrive_cluster(xb, (uint32_t)h);
           c_mbar_arrive_cluster(xb, (uint32_t)peer);
+          TL(15);
         }
       }
     }
@@ -235,8 +246,10 @@ melspec_roles_kernel(const ChainArgs a) {
 
     for (int j = 0; j < J; ++j) {
       c_named_bar(1, kRBuild);   // every warp has finished reading y / w_amax of pair j - 1
+      if (bwarp == 0) TL(0);
       // ---- difference of pair j's electrode rows into y; per-warp max|y| (NaN if any NaN)
       c_mbar_wait(load_bar, j & 1);
+      if (bwarp == 0) TL(1);
       {
         const float4* sa = reinterpret_cast<const float4*>(stage);
         const float4* sb = reinterpret_cast<const float4*>(stage + kCStageFloats);
@@ -254,6 +267,7 @@ melspec_roles_kernel(const ChainArgs a) {
         if (lane == 0) c_mbar_arrive(stage_free);   // the loader may fetch pair j + 1
       }
       c_named_bar(1, kRBuild);   // y and w_amax are final
+      if (bwarp == 0) TL(2);
       float amax = sh.w_amax[0];
 #pragma unroll
       for (int w = 1; w < kRBuildWarps; ++w) amax = max_nan(amax, sh.w_amax[w]);
@@ -303,6 +317,7 @@ melspec_roles_kernel(const ChainArgs a) {
       if (btid == 0) sh.e_tile[j & 3] = e_j;
 
       if (j >= 1) c_mbar_wait(mma_bar0 + 8 * ((j - 1) & 1), ((j - 1) >> 1) & 1);   // operand tiles are free
+      if (bwarp == 0) TL(3);
       {   // operand build: E = s(y[c+m] + y[c-m]), O = s(y[c+m] - y[c-m]) as fp16 hi/lo
         const float* yc = ybuf + kCMargin + (128 * h + t_frame) * a.hop - seg_lo;
 #pragma unroll
@@ -345,6 +360,7 @@ melspec_roles_kernel(const ChainArgs a) {
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
       __syncwarp();
       if (lane == 0) c_mbar_arrive(ops_bar);
+      if (bwarp == 0) TL(4);
     }
   } else {
     // ============================================================================= epilogue group
@@ -371,6 +387,7 @@ melspec_roles_kernel(const ChainArgs a) {
     // pair's clip level, then hand accumulator buffer n & 1 back to the MMA warp.
     auto fold_tile = [&](int n) {
       c_mbar_wait_cluster(xch_bar0 + 8 * (n & 1), (uint32_t)((n >> 1) & 1));
+      { const int j = n + 1; if (warp == 0) TL(9); }
       const float r_pair = fmaxf(fmaxf(sh.xch[n & 1][0], sh.xch[n & 1][1]), a.log2_amin);
       const float off = 2.f * (float)e_prev;          // e_prev = pre-scale exponent of tile n
       const float t_clip = fmaxf(a.log2_amin, r_pair - a.top_log2) + off;
@@ -400,13 +417,16 @@ melspec_roles_kernel(const ChainArgs a) {
       c_mbar_wait(mma_bar0 + 8 * (j & 1), (j >> 1) & 1);
       asm volatile("tcgen05.fence::after_thread_sync;" ::);
       const int e_j = sh.e_tile[j & 3];
+      if (warp == 0) TL(8);
       if (j >= 1) fold_tile(j - 1);
+      if (warp == 0) TL(10);
       if (j % a.ppc == 0) {   // first pair of an item: write the finished one, start afresh
         if (j > 0) flush(j - 1);
 #pragma unroll
         for (int i = 0; i < kMels; ++i) acc[i] = 0.f;
         csum = 0.f;
       }
+      if (warp == 0) TL(11);
       const uint32_t lane_addr = lane_base + (j & 1) * kCAccCols;
       const uint32_t qaddr = lane_addr + qcol;
       float vmax = 0.f;
@@ -435,6 +455,7 @@ melspec_roles_kernel(const ChainArgs a) {
       }
       CH_PARK(kMels / 8 - 1)
       c_tmem_wait_st();
+      if (warp == 0) TL(12);
 #undef CH_PART
 #undef CH_LOAD
 #undef CH_POW
@@ -463,6 +484,7 @@ melspec_roles_kernel(const ChainArgs a) {
       if (lane == 0) sh.w_vmax[j & 1][warp] = c_lg2(vmax) - 2.f * (float)e_j;
       __syncwarp();
       if (lane == 0) c_mbar_arrive(epi_done0 + 8 * (j & 1));   // the publisher may exchange the maximum of tile j
+      if (warp == 0) TL(13);
       e_prev = e_j;
     }
 
@@ -501,8 +523,26 @@ int melspec_roles_run(const ChainArgs& a, long long clusters, cudaStream_t st) {
     configured[dev] = true;
   }
   static const int nq = [] { const char* v = getenv("EEGSPEC_ROLES_NQ"); return (v && v[0] == '2') ? 2 : 4; }();
-  if (nq == 2) melspec_roles_kernel<2><<<(unsigned)(2 * clusters), 128 * 2 + kRBuild + 128, smem, st>>>(a);
-  else melspec_roles_kernel<4><<<(unsigned)(2 * clusters), 128 * 4 + kRBuild + 128, smem, st>>>(a);
+  // EEGSPEC_TIMELINE=<file>: debug only -- synchronous launch that dumps clock stamps of the
+  // pipeline hand-offs of CTAs 0 and 1 (kTlTiles tiles from EEGSPEC_TIMELINE_J0) as raw int64.
+  const char* tl_path = getenv("EEGSPEC_TIMELINE");
+  ChainArgs b = a;
+  const size_t tl_bytes = sizeof(long long) * 2 * kTlTiles * kTlSlots;
+  if (tl_path) {
+    const char* j0 = getenv("EEGSPEC_TIMELINE_J0");
+    b.tl_j0 = j0 ? atoi(j0) : 0;
+    if (cudaMalloc(&b.tl, tl_bytes) != cudaSuccess) return EEGSPEC_EWORKSPACE;
+    cudaMemsetAsync(b.tl, 0, tl_bytes, st);
+  }
+  if (nq == 2) melspec_roles_kernel<2><<<(unsigned)(2 * clusters), 128 * 2 + kRBuild + 128, smem, st>>>(b);
+  else melspec_roles_kernel<4><<<(unsigned)(2 * clusters), 128 * 4 + kRBuild + 128, smem, st>>>(b);
+  if (tl_path) {
+    std::vector<long long> hbuf(2 * kTlTiles * kTlSlots);
+    cudaStreamSynchronize(st);
+    cudaMemcpy(hbuf.data(), b.tl, tl_bytes, cudaMemcpyDeviceToHost);
+    cudaFree(b.tl);
+    if (FILE* f = fopen(tl_path, "wb")) { fwrite(hbuf.data(), 1, tl_bytes, f); fclose(f); }
+  }
   return (int)cudaGetLastError();
 }
 
