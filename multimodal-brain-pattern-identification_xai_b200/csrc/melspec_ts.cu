@@ -49,7 +49,8 @@ constexpr int kTXN = 8;                              // MMA N of the extra-frame
 constexpr int kTXTileBytes = kTXN * kFold * 2;       // 1 024: 8 rows x 64 fp16
 constexpr int kTBuildWarps = 8, kTBuild = 32 * kTBuildWarps;
 constexpr int kTEpiWarps = 16, kTEpi = 32 * kTEpiWarps, kTMels = 32;
-constexpr int kTMmaWarp = kTEpiWarps + kTBuildWarps, kTLoadWarp = kTMmaWarp + 1;
+constexpr int kTMmaWarp = kTEpiWarps + kTBuildWarps, kTLoadWarp = kTMmaWarp + 1, kTDiffWarp0 = kTMmaWarp + 2;
+constexpr int kTDiff = 64;   // two difference warps
 constexpr int kTThreads = kTEpi + kTBuild + 128;
 constexpr int kTYFloats = kCStageFloats + 2 * kCMargin + 128;
 constexpr int kTlTilesT = 64, kTlSlotsT = 32;
@@ -60,13 +61,14 @@ static_assert(kTXCol + 4 * kTXN <= 512, "tensor memory budget");
 static_assert(MELGEN_COL0_P4_3 + 8 * MELGEN_CHUNKS_P4_3 <= kTBins, "the generated epilogue stays inside N");
 
 struct TsShared {
-  unsigned long long load_bar, stage_free, ops_bar[2], afree_bar[2], mma_bar[2], tmem_free[2], xch_bar[2];
+  unsigned long long load_bar, stage_free, y_ready[2], y_free[2], ops_bar[2], afree_bar[2], mma_bar[2], tmem_free[2], xch_bar[2];
   uint32_t tmem_base;
   unsigned int xmax[4];             // this CTA's maximum of tile j (order-preserving uint of log2), [j & 3]
   __align__(16) float pv[2][kTEpiWarps];   // the peer's per-warp maxima of tile j (log2), [j & 1], written by st.async
   int e_tile[4];                    // power-of-two pre-scale exponent of tile j, [j & 3]
-  float w_amax[kTBuildWarps];       // per-warp max|y| of the pair being differenced (NaN if any NaN)
-  float red[kTBuildWarps];
+  float w_amax[2][2];               // per diff warp max|y| of the pair in y buffer j & 1 (NaN if any NaN)
+  float amax_fin[2];                // max|y| after the NaN fill, [j & 1]
+  float red[2];
   float px[2][kCMaxExtra * 128];    // power spectrum of the extra frames [j & 1][frame][bin slot]
   int mel_k0[kMaxMels];
   float mel_w0[kMaxMels], mel_w1[kMaxMels];
@@ -133,11 +135,12 @@ __device__ __forceinline__ void t_st_async_peer(uint32_t local_addr, uint32_t lo
                : "memory");
 }
 
+template <bool kTimeline>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTThreads, 1) melspec_ts_kernel(const ChainArgs a) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   unsigned char* tab = smem_raw;                                       // Ch | Cl | Sh | Sl
   float* ybuf = reinterpret_cast<float*>(tab + 4 * kCTabBytes);        // kTYFloats
-  float* stage = ybuf + kTYFloats;                                     // 2 x kCStageFloats
+  float* stage = ybuf + 2 * kTYFloats;                                 // 2 x kCStageFloats (ybuf is double buffered)
   unsigned char* xt = reinterpret_cast<unsigned char*>(stage + 2 * kCStageFloats);   // [j & 1]{Exh | Oxh}
   __shared__ TsShared sh;
 
@@ -151,7 +154,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTThreads, 1) melspe
   if (J == 0) return;   // both CTAs of the cluster agree
 #define TL(slot)                                                                                             \
   do {                                                                                                       \
-    if (a.tl != nullptr && blockIdx.x < 2 && lane == 0 && j >= a.tl_j0 && j < a.tl_j0 + kTlTilesT)           \
+    if (kTimeline && blockIdx.x < 2 && lane == 0 && j >= a.tl_j0 && j < a.tl_j0 + kTlTilesT)                 \
       a.tl[((blockIdx.x * kTlTilesT + (j - a.tl_j0)) * kTlSlotsT) + (slot)] = clock64();                     \
   } while (0)
 
@@ -165,9 +168,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTThreads, 1) melspe
   }
   if (tid == 32) {
     c_mbar_init(load_bar, 1);
-    c_mbar_init(stage_free, kTBuildWarps);
+    c_mbar_init(stage_free, 2);
     for (int b = 0; b < 2; ++b) {
       c_mbar_init(ops_bar0 + 8 * b, kTBuildWarps);
+      c_mbar_init(c_smem_u32(&sh.y_ready[b]), 2);
+      c_mbar_init(c_smem_u32(&sh.y_free[b]), kTBuildWarps);
       c_mbar_init(afree0 + 8 * b, 1);
       c_mbar_init(mma_bar0 + 8 * b, 1);
       c_mbar_init(tmem_free0 + 8 * b, kTEpiWarps);
@@ -181,7 +186,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTThreads, 1) melspe
     uint4* dst = reinterpret_cast<uint4*>(tab);
     for (int i = tid; i < 4 * kCTabBytes / 16; i += blockDim.x) dst[i] = __ldg(src + i);
     float4* yz = reinterpret_cast<float4*>(ybuf);
-    for (int i = tid; i < kTYFloats / 4; i += blockDim.x) yz[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int i = tid; i < 2 * kTYFloats / 4; i += blockDim.x) yz[i] = make_float4(0.f, 0.f, 0.f, 0.f);
     uint4* xz = reinterpret_cast<uint4*>(xt);
     for (int i = tid; i < 4 * kTXTileBytes / 16; i += blockDim.x) xz[i] = make_uint4(0u, 0u, 0u, 0u);
     for (int i = tid; i < a.n_mels; i += blockDim.x) {
@@ -297,6 +302,90 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTThreads, 1) melspe
           issue_load(j + 1);
         }
       }
+    } else {
+      // ---- difference warps (2 x 32 threads): electrode difference of pair j into y buffer
+      //      j & 1, max|y| (NaN if any NaN), NaN fill, reflect margins -- one tile ahead of the
+      //      build group, which only reads y
+      const int dtid = tid - 32 * kTDiffWarp0, dw = warp - kTDiffWarp0;
+      const uint32_t y_ready0 = c_smem_u32(&sh.y_ready[0]), y_free0 = c_smem_u32(&sh.y_free[0]);
+      auto pair_max_nan = [&](float v) {   // over both warps
+        v = warp_max_nan(v);
+        if (lane == 0) sh.red[dw] = v;
+        c_named_bar(7, kTDiff);
+        const float r = max_nan(sh.red[0], sh.red[1]);
+        c_named_bar(7, kTDiff);
+        return r;
+      };
+      auto pair_sum = [&](float v) {
+        v = warp_sum(v);
+        if (lane == 0) sh.red[dw] = v;
+        c_named_bar(7, kTDiff);
+        const float r = sh.red[0] + sh.red[1];
+        c_named_bar(7, kTDiff);
+        return r;
+      };
+      for (int j = 0; j < J; ++j) {
+        float* yb = ybuf + (j & 1) * kTYFloats;
+        c_mbar_wait(load_bar, j & 1);
+        if (dw == 0) TL(0);
+        if (j >= 2) c_mbar_wait(y_free0 + 8 * (j & 1), ((j - 2) >> 1) & 1);   // the build group has read pair j - 2
+        if (dw == 0) TL(1);
+        float amax = 0.f;
+        {
+          const float4* sa = reinterpret_cast<const float4*>(stage);
+          const float4* sb = reinterpret_cast<const float4*>(stage + kCStageFloats);
+          float4* yd = reinterpret_cast<float4*>(yb + kCMargin);
+#pragma unroll 4
+          for (int i = dtid; i < (seg_n >> 2); i += kTDiff) {
+            const float4 x = sa[i], y = sb[i];
+            const float4 d = make_float4(x.x - y.x, x.y - y.y, x.z - y.z, x.w - y.w);
+            yd[i] = d;
+            amax = max_nan(max_nan(amax, fabsf(d.x)), max_nan(fabsf(d.y), max_nan(fabsf(d.z), fabsf(d.w))));
+          }
+          __syncwarp();
+          if (lane == 0) c_mbar_arrive(stage_free);   // the loader may fetch pair j + 1
+        }
+        amax = pair_max_nan(amax);
+        if (amax != amax) {
+          // NaN samples (rare).  cfg_utils.py:380-385 on the difference: nanmean over the whole
+          // crop, all-NaN -> 0.  Each CTA re-reads both full rows, so no exchange is needed and
+          // both halves get the identical fill value.
+          int rec;
+          const int pr = pair_of(j, rec);
+          const float* ra = a.eeg + rec * a.rec_stride + a.pair_a[pr] * a.ch_stride + a.crop_off;
+          const float* rb = a.eeg + rec * a.rec_stride + a.pair_b[pr] * a.ch_stride + a.crop_off;
+          float s_ = 0.f, c_ = 0.f;
+          for (int i = dtid; i < a.crop; i += kTDiff) {
+            const float d = __ldg(ra + i) - __ldg(rb + i);
+            if (d != d) c_ += 1.f; else s_ += d;
+          }
+          s_ = pair_sum(s_);
+          c_ = pair_sum(c_);
+          const bool all_nan = c_ >= (float)a.crop;
+          const float fill = all_nan ? 0.f : s_ / ((float)a.crop - c_);
+          float m = 0.f;
+          for (int i = dtid; i < seg_n; i += kTDiff) {
+            float d = yb[kCMargin + i];
+            if (all_nan) d = 0.f; else if (d != d) d = fill;
+            yb[kCMargin + i] = d;
+            m = fmaxf(m, fabsf(d));
+          }
+          amax = pair_max_nan(m);
+        }
+        if (a.pad_mode == 1) {   // reflect padding (librosa < 0.10); zero padding is the resident state
+          for (int k = dtid; k < 2 * kCMargin + 128; k += kTDiff) {
+            const int idx = k < kCMargin ? k : seg_n + k;          // left margin | right margin
+            const int i = seg_lo + idx - kCMargin;                 // crop coordinate
+            const int src = i < 0 ? -i : (i >= a.crop ? 2 * (a.crop - 1) - i : -1);
+            const int sidx = src - seg_lo;
+            if (idx < kTYFloats) yb[idx] = (src >= 0 && sidx >= 0 && sidx < seg_n) ? yb[kCMargin + sidx] : 0.f;
+          }
+        }
+        if (dtid == 0) sh.amax_fin[j & 1] = amax;
+        __syncwarp();
+        if (lane == 0) c_mbar_arrive(y_ready0 + 8 * (j & 1));
+        if (dw == 0) TL(2);
+      }
     }
   } else if (warp >= kTEpiWarps) {
     // ================================================================================ build group
@@ -306,100 +395,22 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTThreads, 1) melspe
     const int btid = tid - kTEpi, bwarp = warp - kTEpiWarps;
     const int t_frame = btid & (kTileFrames - 1), part = btid >> 7;
     const uint32_t ring_addr = tmem_base + ((uint32_t)(32 * (warp & 3)) << 16) + kTRingCol + 4 * part;
-    auto grp_max_nan = [&](float v) {
-      v = warp_max_nan(v);
-      if (lane == 0) sh.red[bwarp] = v;
-      c_named_bar(1, kTBuild);
-      float r = sh.red[0];
-#pragma unroll
-      for (int w = 1; w < kTBuildWarps; ++w) r = max_nan(r, sh.red[w]);
-      c_named_bar(1, kTBuild);
-      return r;
-    };
-    auto grp_sum = [&](float v) {
-      v = warp_sum(v);
-      if (lane == 0) sh.red[bwarp] = v;
-      c_named_bar(1, kTBuild);
-      float r = 0.f;
-#pragma unroll
-      for (int w = 0; w < kTBuildWarps; ++w) r += sh.red[w];
-      c_named_bar(1, kTBuild);
-      return r;
-    };
+    const uint32_t y_ready0 = c_smem_u32(&sh.y_ready[0]), y_free0 = c_smem_u32(&sh.y_free[0]);
 
     for (int j = 0; j < J; ++j) {
-      c_named_bar(1, kTBuild);   // every warp has finished reading y / w_amax of pair j - 1
-      if (bwarp == 0) TL(0);
-      // ---- difference of pair j's electrode rows into y; per-warp max|y| (NaN if any NaN)
-      c_mbar_wait(load_bar, j & 1);
-      if (bwarp == 0) TL(1);
-      {
-        const float4* sa = reinterpret_cast<const float4*>(stage);
-        const float4* sb = reinterpret_cast<const float4*>(stage + kCStageFloats);
-        float4* yd = reinterpret_cast<float4*>(ybuf + kCMargin);
-        float amax = 0.f;
-        for (int i = btid; i < (seg_n >> 2); i += kTBuild) {
-          const float4 x = sa[i], y = sb[i];
-          const float4 d = make_float4(x.x - y.x, x.y - y.y, x.z - y.z, x.w - y.w);
-          yd[i] = d;
-          amax = max_nan(max_nan(amax, fabsf(d.x)), max_nan(fabsf(d.y), max_nan(fabsf(d.z), fabsf(d.w))));
-        }
-        amax = warp_max_nan(amax);
-        if (lane == 0) sh.w_amax[bwarp] = amax;
-        __syncwarp();
-        if (lane == 0) c_mbar_arrive(stage_free);   // the loader may fetch pair j + 1
-      }
-      c_named_bar(1, kTBuild);   // y and w_amax are final
-      if (bwarp == 0) TL(2);
-      float amax = sh.w_amax[0];
-#pragma unroll
-      for (int w = 1; w < kTBuildWarps; ++w) amax = max_nan(amax, sh.w_amax[w]);
-      if (amax != amax) {
-        // NaN samples (rare).  cfg_utils.py:380-385 on the difference: nanmean over the whole
-        // crop, all-NaN -> 0.  Each CTA re-reads both full rows, so no exchange is needed and
-        // both halves get the identical fill value.
-        int rec;
-        const int pr = pair_of(j, rec);
-        const float* ra = a.eeg + rec * a.rec_stride + a.pair_a[pr] * a.ch_stride + a.crop_off;
-        const float* rb = a.eeg + rec * a.rec_stride + a.pair_b[pr] * a.ch_stride + a.crop_off;
-        float s_ = 0.f, c_ = 0.f;
-        for (int i = btid; i < a.crop; i += kTBuild) {
-          const float d = __ldg(ra + i) - __ldg(rb + i);
-          if (d != d) c_ += 1.f; else s_ += d;
-        }
-        s_ = grp_sum(s_);
-        c_ = grp_sum(c_);
-        const bool all_nan = c_ >= (float)a.crop;
-        const float fill = all_nan ? 0.f : s_ / ((float)a.crop - c_);
-        float m = 0.f;
-        for (int i = btid; i < seg_n; i += kTBuild) {
-          float d = ybuf[kCMargin + i];
-          if (all_nan) d = 0.f; else if (d != d) d = fill;
-          ybuf[kCMargin + i] = d;
-          m = fmaxf(m, fabsf(d));
-        }
-        amax = grp_max_nan(m);
-      }
-      if (a.pad_mode == 1) {   // reflect padding (librosa < 0.10); zero padding is the resident state
-        for (int k = btid; k < 2 * kCMargin + 128; k += kTBuild) {
-          const int idx = k < kCMargin ? k : seg_n + k;          // left margin | right margin
-          const int i = seg_lo + idx - kCMargin;                 // crop coordinate
-          const int src = i < 0 ? -i : (i >= a.crop ? 2 * (a.crop - 1) - i : -1);
-          const int sidx = src - seg_lo;
-          if (idx < kTYFloats) ybuf[idx] = (src >= 0 && sidx >= 0 && sidx < seg_n) ? ybuf[kCMargin + sidx] : 0.f;
-        }
-        c_named_bar(1, kTBuild);
-      }
+      c_mbar_wait(y_ready0 + 8 * (j & 1), (j >> 1) & 1);   // y buffer j & 1 and its max|y| are final
+      const float* yb = ybuf + (j & 1) * kTYFloats;
+      const float amax = sh.amax_fin[j & 1];
       int e_j = 0;   // exact power-of-two pre-scale: amax * 2^e in [2^10, 2^11)
       {
-        int ex = 0;
-        if (amax > 0.f && amax < __int_as_float(0x7f800000)) { frexpf(amax, &ex); e_j = 11 - ex; }
+        const int ef = (int)((__float_as_uint(amax) >> 23) & 0xffu);   // biased exponent; 0 = zero / subnormal, 255 = inf / NaN
+        if (ef > 0 && ef < 255) e_j = 137 - ef;                        // 11 - (ef - 126)
         e_j = max(-60, min(60, e_j));
       }
       const float s = __int_as_float((127 + e_j) << 23);
       if (btid == 0) sh.e_tile[j & 3] = e_j;
 
-      const float* yc = ybuf + kCMargin + (128 * h + t_frame) * a.hop - seg_lo;
+      const float* yc = yb + kCMargin + (128 * h + t_frame) * a.hop - seg_lo;
 #pragma unroll 1
       for (int ks = 0; ks < kFold / 16; ++ks) {
         const int g = 4 * j + ks, slot = ks & 1;   // slot = g & 1
@@ -420,6 +431,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTThreads, 1) melspe
           c_split2(ov[0], ov[1], oh.x, ol.x); c_split2(ov[2], ov[3], oh.y, ol.y);
           c_split2(ov[4], ov[5], oh.z, ol.z); c_split2(ov[6], ov[7], oh.w, ol.w);
         }
+        if (ks == kFold / 16 - 1) {   // last read of y buffer j & 1 (the extra frames were read at ks == 0)
+          __syncwarp();
+          if (lane == 0) c_mbar_arrive(y_free0 + 8 * (j & 1));
+        }
         if (ks >= 2 && bwarp == 0) TL(16 + 4 * (ks - 2));
         if (g >= 2) c_mbar_wait(afree0 + 8 * slot, (uint32_t)(((ks >> 1) + 1) & 1));   // ((g - 2) >> 1) & 1: the MMAs of step g - 2 have read the slot
         if (ks == 0 && bwarp == 0) TL(3);
@@ -430,7 +445,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTThreads, 1) melspe
           // operand in shared memory, hi halves only; the MMAs of tile j - 2 that read this
           // buffer completed before the commit waited for above.
           const int x = btid >> 6, m = btid & (kFold - 1);
-          const float* yx = ybuf + kCMargin + (a.n_time + x) * a.hop - seg_lo;
+          const float* yx = yb + kCMargin + (a.n_time + x) * a.hop - seg_lo;
           const float yp = yx[m], yms = yx[-m] * s;
           const float e = fmaf(yp, s, yms), o = fmaf(yp, s, -yms);
           const int off = (j & 1) * 2 * kTXTileBytes + c_umma_offset(x, m);
@@ -475,7 +490,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTThreads, 1) melspe
     // pair's clip level, then hand accumulator buffer n & 1 back to the MMA warp.
     auto fold_tile = [&](int n) {
       c_mbar_wait(xch_bar0 + 8 * (n & 1), (uint32_t)((n >> 1) & 1));
-      { const int j = n + 1; if (warp == 0) TL(9); }
+      { const int j = n; if (warp == 0) TL(9); }
       float r_pair = fmaxf(t_ord2f(sh.xmax[n & 3]), a.log2_amin);
       {
         const float4* pv = reinterpret_cast<const float4*>(sh.pv[n & 1]);
@@ -545,27 +560,17 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTThreads, 1) melspe
       *reinterpret_cast<float4*>(r + 3 * mstride) = make_float4(tv[0].w, tv[1].w, tv[2].w, tv[3].w);
     };
 
+    // Per tile: main (power, mel, lg2, park) -> contribute the maximum -> wait for the exchange
+    // -> fold the parked values and hand the accumulator buffer back.  The fold comes LAST: the
+    // MMAs of tile j + 2 wait for this buffer while those of tile j + 1 already run in the other
+    // one, so the tensor pipe and the operand build overlap the whole epilogue of tile j
+    // (folding at the start of the next tile's epilogue put the exchange latency and the fold on
+    // the critical loop: period = fold + MMA chain instead of max(epilogue, MMA chain)).
     for (int j = 0; j < J; ++j) {
       c_mbar_wait(mma_bar0 + 8 * (j & 1), (j >> 1) & 1);
       asm volatile("tcgen05.fence::after_thread_sync;" ::);
       const int e_j = sh.e_tile[j & 3];
       if (warp == 0) TL(8);
-      // transposition schedule: record number q (of this cluster) is complete after the chain_done
-      // of tile 16 (q + 1); its group g is handled in tile 16 (q + 1) + 2 g + 2
-      const int k_tr = j - 1, q_tr = k_tr / tpi - 1, step = k_tr & (tpi - 1);
-      const bool tr_now = q_tr >= 0 && (step & 1);
-      const int rec_prev = cluster_id + q_tr * n_clusters;
-      if (tr_now) transpose_load(rec_prev, step >> 1);
-      if (j >= 1) fold_tile(j - 1);
-      if (warp == 0) TL(10);
-      if (j % a.ppc == 0) {   // first pair of a chain: store the finished one, start afresh
-        if (j > 0) chain_done(j - 1);
-#pragma unroll
-        for (int i = 0; i < kTMels; ++i) acc[i] = 0.f;
-        csum = 0.f;
-      }
-      if (tr_now) transpose_store(rec_prev, step >> 1);
-      if (warp == 0) TL(11);
       const uint32_t lane_addr = lane_base + (j & 1) * kTAcc;
       const uint32_t qaddr = lane_addr + qcol;
       float vmax = 0.f;
@@ -635,16 +640,24 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTThreads, 1) melspe
       __syncwarp();
       if (warp == 0) TL(13);
       e_prev = e_j;
+      // transposition schedule: record number q (of this cluster) is completely stashed by the
+      // end of tile 16 q + 15; its group g is handled in tile 16 (q + 1) + 2 g + 1
+      const int q_tr = j / tpi - 1, step = j & (tpi - 1);
+      const bool tr_now = q_tr >= 0 && (step & 1);
+      const int rec_prev = cluster_id + q_tr * n_clusters;
+      if (tr_now) transpose_load(rec_prev, step >> 1);   // L2 latency covered by the exchange wait and the fold
+      fold_tile(j);
+      if (warp == 0) TL(10);
+      if ((j + 1) % a.ppc == 0) {   // last pair of a chain: stash it, start afresh
+        chain_done(j);
+#pragma unroll
+        for (int i = 0; i < kTMels; ++i) acc[i] = 0.f;
+        csum = 0.f;
+      }
+      if (tr_now) transpose_store(rec_prev, step >> 1);
+      if (warp == 0) TL(11);
     }
-
-    // ---- the last pair's maximum has been exchanged: fold it and write the last chain
-    fold_tile(J - 1);
-    chain_done(J - 1);
-    if (n_my_items >= 2) {   // the last group of the record before the last one
-      const int rec_b = cluster_id + (n_my_items - 2) * n_clusters;
-      transpose_load(rec_b, 7);
-      transpose_store(rec_b, 7);
-    }
+    // ---- the last record of this cluster: all groups at once
     {
       const int rec_last = cluster_id + (n_my_items - 1) * n_clusters;
       for (int g = 0; g < kTMels / 4; ++g) {
@@ -664,7 +677,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTThreads, 1) melspe
 
 // ------------------------------------------------------------------------------------- host
 size_t melspec_ts_smem_bytes() {
-  return 4 * (size_t)kCTabBytes + sizeof(float) * ((size_t)kTYFloats + 2 * (size_t)kCStageFloats) + 4 * (size_t)kTXTileBytes;
+  return 4 * (size_t)kCTabBytes + sizeof(float) * (2 * (size_t)kTYFloats + 2 * (size_t)kCStageFloats) + 4 * (size_t)kTXTileBytes;
 }
 
 // Launches the TS kernel on `clusters` clusters of two CTAs; `a.n_items` must be the number of
@@ -678,7 +691,9 @@ int melspec_ts_run(const ChainArgs& a, long long clusters, cudaStream_t st) {
   if (dev < 0 || dev >= 64) return EEGSPEC_EUNSUPPORTED;
   const size_t smem = melspec_ts_smem_bytes();
   if (!configured[dev]) {
-    const cudaError_t e = cudaFuncSetAttribute(melspec_ts_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = cudaFuncSetAttribute(melspec_ts_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return (int)e;
+    e = cudaFuncSetAttribute(melspec_ts_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return (int)e;
     configured[dev] = true;
   }
@@ -693,7 +708,8 @@ int melspec_ts_run(const ChainArgs& a, long long clusters, cudaStream_t st) {
     if (cudaMalloc(&b.tl, tl_bytes) != cudaSuccess) return EEGSPEC_EWORKSPACE;
     cudaMemsetAsync(b.tl, 0, tl_bytes, st);
   }
-  melspec_ts_kernel<<<(unsigned)(2 * clusters), kTThreads, smem, st>>>(b);
+  if (tl_path) melspec_ts_kernel<true><<<(unsigned)(2 * clusters), kTThreads, smem, st>>>(b);
+  else melspec_ts_kernel<false><<<(unsigned)(2 * clusters), kTThreads, smem, st>>>(b);
   if (tl_path) {
     std::vector<long long> hbuf(2 * kTlTilesT * kTlSlotsT);
     cudaStreamSynchronize(st);
