@@ -263,9 +263,9 @@ def main():
     achieved_n = RECORDS * BYTES_N / per_launch_s / 1e9
     roofline = {
         "bound": "hbm", "achieved": achieved_n, "peak": peak, "unit": "GB/s", "frac": achieved_n / peak,
-        "traffic": committed_traffic("melspec_roles_dram_bytes_per_launch"),
+        "traffic": committed_traffic("melspec_ts_dram_bytes_per_launch"),
         "peak_source": peak_src,
-        "kernel": "melspec_roles_kernel (engine 3, role-split: one persistent clustered launch per step; "
+        "kernel": "melspec_ts_kernel (engine 3, frame operand in tensor memory: one persistent clustered launch per step; "
                   "algorithmic bytes 1 324 288 B/record x 1024 records per launch)",
         "note": "co-bound by issue slots / MUFU / tensor pipe, not by HBM alone (DESIGN.md 3.2)",
     }

@@ -23,7 +23,7 @@ cap() {  # name regex skip
       -f -o $OUT/prof_${TAG}_$1 $CMD > $OUT/ncu_$1_$TAG.log 2>&1
   echo "capture $1 rc=$?"
 }
-cap melspec_roles melspec_roles_kernel 3
+cap melspec_ts melspec_ts_kernel 3
 cap stft_hms50s stft_image_kernel 3
 cap stft_diffeeg stft_image_kernel 8
 ls -la $OUT

@@ -66,6 +66,22 @@ def test_engines_agree_at_size():
     assert np.abs(a - b).max() <= 2e-4 and np.abs(c - b).max() <= 2e-4
 
 
+def test_clip_level_and_last_frame_maximum():
+    """A loud burst in the last 40 samples puts the pair maximum into frame 256 (beyond the kept
+    width) and most of the image more than 80 dB below it: exercises the frames that only feed
+    the maximum and the deferred clip (the speculative no-clip pass must be corrected).  A
+    second record has the burst in the middle (clip without the extra frame)."""
+    rng = np.random.default_rng(29)
+    x = eeg_like(rng, (3, 20, 10000)) * np.float32(1e-2)
+    x[0, :, -40:] += (rng.standard_normal((20, 40)) * 3e3).astype(np.float32)
+    x[1, :, 5000:5100] += (rng.standard_normal((20, 100)) * 3e3).astype(np.float32)
+    want = mo.eeg_to_spectrogram_batch_oracle(x)
+    assert (want[0] <= -1.0 + 1e-6).mean() > 0.3 and (want[1] <= -1.0 + 1e-6).mean() > 0.3   # clipped pixels exist
+    for engine in (3, 1):
+        err = np.abs(run(x, engine=engine) - want).max()
+        assert err <= ATOL, f"engine {engine}: max abs err {err:.3e}"
+
+
 def test_single_record_time_major_and_crop():
     rng = np.random.default_rng(22)
     x = eeg_like(rng, (20, 18000))                           # 90 s: middle 50 s is used
