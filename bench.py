@@ -315,6 +315,28 @@ def main():
                                      "kernel": "stft_image_kernel<6,0>, 5 168 000 B/record"}},
         }
 
+    if "r" in legs:
+        # ------------------------------------------------------------ row (f)1: raw-EEG transformer
+        x_xf = torch.randn((RECORDS, 10000, 20), device="cuda", generator=torch.Generator(device="cuda").manual_seed(7)) * 40.0
+        xf = b200spec.EEGTransformer(n_feats=19, downsample=5)
+
+        def step_xf():
+            keep["xf"] = xf.transform(x_xf)
+
+        ms_xf, _ = timed(step_xf, args.steps, 3)
+        keep.pop("xf", None)
+        del x_xf
+        torch.cuda.empty_cache()
+        bytes_xf = 4 * 10000 * 20 + 4 * 2000 * 19
+        a_xf = RECORDS * bytes_xf / (ms_xf * 1e-3 / args.steps) / 1e9
+        result["eeg_transform"] = {
+            "what": "_EEGTransformer.transform drop-in (row f1; reference-pinned parity): select 19 / clip / NaN->0 / "
+                    "/32 / Butterworth-4 lfilter / decimate 5, one kernel per call",
+            "workload": "(1024,10000,20)->(1024,2000,19) per GPU, 819 MB in per step (> L2)",
+            "value": world * RECORDS * args.steps / (ms_xf * 1e-3), "unit": UNIT, "ms_per_step": ms_xf / args.steps,
+            "roofline": {"bound": "hbm", "achieved": a_xf, "peak": peak, "unit": "GB/s", "frac": a_xf / peak, "traffic": None,
+                         "kernel": f"eeg_transform_kernel<5,1,1,0>, {bytes_xf} B/record"}}
+
     if "e2e" in legs:
         # ------------------------------------------------------------ end to end: host buffers in and out
         x_n = None
@@ -359,7 +381,13 @@ def main():
             c_n = arm.run("n", n_rec, seed=2)
             c_r = arm.run("r10", max(arm.cores * 16, 128), seed=5)
             c_r50 = arm.run("r50", max(arm.cores * 4, 32), seed=6)
+            c_xf = arm.run("xf", max(arm.cores * 8, 64), seed=7)
             arm.close()
+            if "eeg_transform" in result:
+                result["eeg_transform"]["cpu_baseline"] = {
+                    "value": c_xf["records_per_s"], "unit": UNIT, "cores": arm.cores, "kind": "port",
+                    "sample": f"{c_xf['records']} records (10000,20) through oracle/eegtransform_oracle.py "
+                              "(the reference's own NumPy / SciPy calls)", "per_core": c_xf["per_core_records_per_s"]}
             result["cpu_baseline"] = {
                 "value": c_n["records_per_s"], "unit": UNIT, "cores": arm.cores, "kind": "port",
                 "sample": f"{c_n['records']} of the 1024 records, mel image via oracle/melspec_oracle.py "

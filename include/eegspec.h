@@ -140,6 +140,44 @@ int eegspec_stft_image_host_f32(const float *x, int64_t rows, int64_t length, in
 int eegspec_melspec_host_f32(const float *eeg, int64_t batch, int32_t n_ch, int64_t length,
                              const eegspec_mel_params *p, float *out, int device);
 
+/* ------------------------------------------------------------------------------------------
+ * Row (f)1 -- the step in front of the path: raw-EEG transformer
+ *   replaces _EEGTransformer.transform, /root/reference/root/src/data/dataset.py:73-104
+ *   (selection :88-90 or "magic 8" differences :106-123, clip +-1024 / NaN -> 0 / divide by 32
+ *   :92-94, Butterworth low-pass as a causal IIR along time :125-131, decimation :101-102).
+ * ------------------------------------------------------------------------------------------ */
+#define EEGSPEC_MAX_XF_CH 32
+#define EEGSPEC_XF_ORDER 4
+
+typedef struct eegspec_xform_params {
+  int32_t n_out;                       /* output channels (19, or 8 for the magic-8 montage)   */
+  int32_t sel_a[EEGSPEC_MAX_XF_CH];    /* output channel c = x[:, sel_a[c]] - x[:, sel_b[c]],   */
+  int32_t sel_b[EEGSPEC_MAX_XF_CH];    /*   sel_b[c] < 0: plain selection x[:, sel_a[c]]        */
+  int32_t normalize;                   /* clip to +-clip_abs, NaN -> 0, multiply by scale       */
+  float clip_abs;                      /* 1024                                                  */
+  float scale;                         /* 1 / 32                                                */
+  int32_t filter;                      /* 1: apply the IIR b / a below (a[0] == 1), 0: skip     */
+  double b[EEGSPEC_XF_ORDER + 1];      /* scipy.signal.butter(4, 0.2) numerator                 */
+  double a[EEGSPEC_XF_ORDER + 1];      /* denominator                                           */
+  int32_t downsample;                  /* keep every downsample-th sample (1 = all), <= 8       */
+  int32_t out_channel_major;           /* 0: out is (batch, L_out, n_out) like the reference;
+                                        * 1: (batch, n_out, L_out), the layout compute_stft eats */
+} eegspec_xform_params;
+
+/* Defaults of CFG.dataset["eeg"] (cfg_utils.py:97-106): 19 selected channels, normalize,
+ * 4th-order 20 Hz Butterworth at 200 Hz (coefficients in double precision), downsample 5. */
+void eegspec_xform_params_default(eegspec_xform_params *p);
+
+/* Output samples per record: ceil(length / downsample). */
+int64_t eegspec_xform_out_length(int64_t length, const eegspec_xform_params *p);
+
+/* x: device fp32, `batch` records of (length, n_ch) TIME-major (the reference's (L, C) arrays),
+ * consecutive records `rec_stride` elements apart, 16-byte aligned, n_ch % 4 == 0.
+ * out: device fp32 (batch, L_out, n_out) or (batch, n_out, L_out), see out_channel_major. */
+int eegspec_eeg_transform_f32(const float *x, int64_t batch, int64_t length, int32_t n_ch,
+                              int64_t rec_stride, const eegspec_xform_params *p, float *out,
+                              void *stream);
+
 /* Number of kernel launches issued by this library since load (bench bookkeeping). */
 int64_t eegspec_launch_count(void);
 

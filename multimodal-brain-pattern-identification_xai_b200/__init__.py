@@ -6,6 +6,7 @@ KC-decoder/Multimodal-Brain-Pattern-Identification_XAI:
 * ``compute_stft(signal, config)``      -- /root/reference/root/src/utils/DiffEEG_utils.py:27-76
 * ``compute_stft_single(signal, config)`` -- DiffEEG_utils.py:504-509
 * ``eeg_to_spectrogram(eeg)``           -- the 4-chain x 128-mel image BASELINE.json names
+* ``EEGTransformer(...).transform(x)``   -- ``_EEGTransformer``, /root/reference/root/src/data/dataset.py:48-104
 * ``install()``                         -- rebinds ``compute_stft`` inside the reference's modules
 
 The directory name is not a Python identifier; ``import b200spec`` (repo root) is the same
@@ -26,6 +27,8 @@ _API = {
     "melspec_geometry": "transform",
     "install": "transform",
     "launch_count": "transform",
+    "EEGTransformer": "eegtransformer",
+    "xform_params": "eegtransformer",
     "shard_bounds": "sharding",
     "shard_slice": "sharding",
     "gather_spectrograms": "sharding",

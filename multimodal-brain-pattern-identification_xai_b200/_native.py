@@ -36,6 +36,18 @@ class MelParams(C.Structure):
     ]
 
 
+MAX_XF_CH = 32
+
+
+class XformParams(C.Structure):
+    _fields_ = [
+        ("n_out", C.c_int32), ("sel_a", C.c_int32 * MAX_XF_CH), ("sel_b", C.c_int32 * MAX_XF_CH),
+        ("normalize", C.c_int32), ("clip_abs", C.c_float), ("scale", C.c_float), ("filter", C.c_int32),
+        ("b", C.c_double * 5), ("a", C.c_double * 5), ("downsample", C.c_int32),
+        ("out_channel_major", C.c_int32),
+    ]
+
+
 # name -> (restype, argtypes); mirrors include/eegspec.h one to one.
 SIGNATURES = {
     "eegspec_abi_version": (C.c_int, []),
@@ -59,6 +71,10 @@ SIGNATURES = {
                                               C.c_int64, C.c_float, C.c_void_p, C.c_int]),
     "eegspec_melspec_host_f32": (C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_int64,
                                            C.POINTER(MelParams), C.c_void_p, C.c_int]),
+    "eegspec_xform_params_default": (None, [C.POINTER(XformParams)]),
+    "eegspec_xform_out_length": (C.c_int64, [C.c_int64, C.POINTER(XformParams)]),
+    "eegspec_eeg_transform_f32": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, C.c_int32, C.c_int64,
+                                            C.POINTER(XformParams), C.c_void_p, C.c_void_p]),
     "eegspec_launch_count": (C.c_int64, []),
 }
 

@@ -242,6 +242,19 @@ int eegspec_melspec_host_f32(const float* eeg, int64_t batch, int32_t n_ch, int6
   return EEGSPEC_OK;
 }
 
+void eegspec_xform_params_default(eegspec_xform_params* p) {
+  if (p) eegspec::xform_params_default(p);
+}
+
+int64_t eegspec_xform_out_length(int64_t length, const eegspec_xform_params* p) {
+  return (p && length > 0) ? eegspec::xform_out_length(length, p) : 0;
+}
+
+int eegspec_eeg_transform_f32(const float* x, int64_t batch, int64_t length, int32_t n_ch, int64_t rec_stride,
+                              const eegspec_xform_params* p, float* out, void* stream) {
+  return eegspec::eeg_transform_launch(x, batch, length, n_ch, rec_stride, p, out, static_cast<cudaStream_t>(stream));
+}
+
 int64_t eegspec_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 
 }  // extern "C"

@@ -33,4 +33,10 @@ int melspec_launch(const float* eeg, long long batch, int n_ch, long long length
                    long long rec_stride, const eegspec_mel_params* p, float* out, void* workspace,
                    size_t workspace_bytes, cudaStream_t st);
 
+// eegtransform.cu
+void xform_params_default(eegspec_xform_params* p);
+long long xform_out_length(long long length, const eegspec_xform_params* p);
+int eeg_transform_launch(const float* x, long long batch, long long length, int n_ch, long long rec_stride,
+                         const eegspec_xform_params* p, float* out, cudaStream_t st);
+
 }  // namespace eegspec

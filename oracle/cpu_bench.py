@@ -31,6 +31,8 @@ def host_cores() -> int:
 def synth_records(mode: str, n: int, seed: int) -> np.ndarray:
     """Same distribution as bench.py's device-side generator (random walk + noise, clipped)."""
     rng = np.random.default_rng(seed)
+    if mode == "xf":   # raw EEG, time-major (L, C) like the reference's parquet windows
+        return (rng.standard_normal((n, 10000, 20), dtype=np.float32) * np.float32(40.0))
     shape = (n, 20, 10000) if mode in ("n", "r50") else (n, 19, 2000)
     x = np.cumsum(rng.standard_normal(shape, dtype=np.float32), axis=-1) * np.float32(0.3)
     x += rng.standard_normal(shape, dtype=np.float32)
@@ -47,7 +49,11 @@ def _work(task):
 
     x = synth_records(mode, n, seed)
     t0 = time.perf_counter()
-    if mode == "n":
+    if mode == "xf":
+        from oracle import eegtransform_oracle
+
+        out = eegtransform_oracle.eeg_transform_batch_oracle(x, n_feats=19, downsample=5)
+    elif mode == "n":
         out = melspec_oracle.eeg_to_spectrogram_batch_oracle(x)
     else:
         out = stft_oracle.compute_stft_port(x, _Cfg)

@@ -66,3 +66,43 @@ def make_config(n_fft: int = 64, hop_length: int = 32, window: str = "hann"):
             "stft_window": window,
         }
     )
+
+
+# --------------------------------------------------------------------------- _EEGTransformer
+_DATASET = os.path.join(REFERENCE_ROOT, "root", "src", "data", "dataset.py")
+_CFG_UTILS = os.path.join(REFERENCE_ROOT, "root", "src", "utils", "cfg_utils.py")
+
+
+def reference_cfg_channels():
+    """``CFG.feats`` / ``CFG.channel_feats`` / ``CFG.EEG_PTS`` read from the literals of
+    ``class CFG`` (/root/reference/root/src/utils/cfg_utils.py:70-96) without importing it."""
+    with open(_CFG_UTILS, "r", encoding="utf-8") as fh:
+        tree = ast.parse(fh.read(), filename=_CFG_UTILS)
+    cfg = next(n for n in tree.body if isinstance(n, ast.ClassDef) and n.name == "CFG")
+    got = {}
+    for node in cfg.body:
+        if isinstance(node, ast.Assign) and len(node.targets) == 1 and isinstance(node.targets[0], ast.Name):
+            name = node.targets[0].id
+            if name in ("feats", "channel_feats", "EEG_FREQ", "EEG_WLEN"):
+                got[name] = ast.literal_eval(node.value)
+    return SimpleNamespace(feats=got["feats"], channel_feats=got["channel_feats"],
+                           EEG_PTS=int(got["EEG_FREQ"] * got["EEG_WLEN"]))
+
+
+def load_reference_eeg_transformer():
+    """The reference ``_EEGTransformer`` class (/root/reference/root/src/data/dataset.py:48-147),
+    lifted out of its module's AST and executed with the names it uses (``np``, SciPy's
+    ``butter`` / ``lfilter``, ``Optional`` and a ``CFG`` holding the reference's own channel lists)."""
+    from typing import Optional
+
+    import numpy as np
+    from scipy.signal import butter, lfilter
+
+    with open(_DATASET, "r", encoding="utf-8") as fh:
+        tree = ast.parse(fh.read(), filename=_DATASET)
+    node = next(n for n in tree.body if isinstance(n, ast.ClassDef) and n.name == "_EEGTransformer")
+    module = ast.Module(body=[node], type_ignores=[])
+    ast.fix_missing_locations(module)
+    env = {"np": np, "butter": butter, "lfilter": lfilter, "Optional": Optional, "CFG": reference_cfg_channels()}
+    exec(compile(module, _DATASET, "exec"), env)  # noqa: S102 - the reference's own code
+    return env["_EEGTransformer"]

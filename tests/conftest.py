@@ -53,3 +53,8 @@ class Cfg:
     def __init__(self, n_fft=64, hop_length=32, window="hann"):
         self.diffEEG_trainer = {"stft_n_fft": n_fft, "stft_hop_length": hop_length,
                                 "stft_window": window}
+
+
+@pytest.fixture(scope="session")
+def eegtransform_golden():
+    return np.load(os.path.join(GOLDEN_DIR, "eegtransform_golden.npz"))

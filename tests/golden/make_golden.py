@@ -11,6 +11,9 @@
   CUDA path and the oracle itself against regressions.  The montage facts inside are read
   from the reference's ``config.yml``.
 
+* ``eegtransform_golden.npz`` -- inputs and outputs of the REFERENCE's own
+  ``_EEGTransformer.transform`` (``dataset.py:73-104``), same mechanism; pins row (f)1.
+
 Versions used to generate the committed files are stored inside them.
 """
 from __future__ import annotations
@@ -118,8 +121,45 @@ def make_melspec():
     print("melspec_golden.npz:", {k: v.shape for k, v in out.items() if "/y" in k})
 
 
+XFORM_CASES = {
+    # name: (L, C, transformer kwargs, kind)
+    "default19": (10000, 20, dict(n_feats=19, downsample=5), "eeg"),
+    "magic8": (10000, 8, dict(n_feats=8, apply_chris_magic_ch8=True, downsample=5), "eeg"),
+    "nan_clip": (4000, 20, dict(n_feats=19, downsample=5), "nan"),
+    "no_downsample": (2000, 20, dict(n_feats=19), "eeg"),
+    "no_filter_ds4": (3001, 20, dict(n_feats=19, apply_butter_lowpass_filter=False, downsample=4), "eeg"),
+    "raw_scale": (2403, 20, dict(n_feats=19, normalize=False, downsample=3), "eeg"),
+}
+
+
+def make_eegtransform():
+    """Inputs and outputs of the REFERENCE's own ``_EEGTransformer.transform``
+    (/root/reference/root/src/data/dataset.py:73-104) through ``oracle/ref_extract.py``."""
+    import scipy
+
+    ref_cls = rx.load_reference_eeg_transformer()
+    rng = np.random.default_rng(20261106)
+    out = {}
+    for name, (length, n_ch, kw, kind) in XFORM_CASES.items():
+        x = (np.cumsum(rng.standard_normal((length, n_ch)), axis=0) * 3.0
+             + 40.0 * rng.standard_normal((length, n_ch))).astype(np.float32)
+        if kind == "nan":
+            x[100:140, 3] = np.nan
+            x[rng.random((length,)) < 0.01, 7] = np.nan
+            x[:, 11] = np.nan                                   # a dead electrode
+            x[2000:2050, 0] = 5000.0                            # beyond the clip level
+            x[2100:2150, 1] = -np.inf
+        out[f"{name}/x"] = x
+        out[f"{name}/y"] = np.asarray(ref_cls(**kw).transform(x), dtype=np.float64)
+    out["versions"] = np.array([f"numpy {np.__version__}", f"scipy {scipy.__version__}"])
+    path = os.path.join(HERE, "eegtransform_golden.npz")
+    np.savez_compressed(path, **out)
+    print("wrote", path, os.path.getsize(path), "bytes")
+
+
 if __name__ == "__main__":
     if not rx.reference_available():
         raise SystemExit("/root/reference is not mounted: golden vectors can only be made in the build container")
     make_stft()
     make_melspec()
+    make_eegtransform()
