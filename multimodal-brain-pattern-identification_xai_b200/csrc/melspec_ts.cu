@@ -69,9 +69,7 @@ struct TsShared {
   float w_amax[2][2];               // per diff warp max|y| of the pair in y buffer j & 1 (NaN if any NaN)
   float amax_fin[2];                // max|y| after the NaN fill, [j & 1]
   float red[2];
-  float px[2][kCMaxExtra * 128];    // power spectrum of the extra frames [j & 1][frame][bin slot]
-  int mel_k0[kMaxMels];
-  float mel_w0[kMaxMels], mel_w1[kMaxMels];
+  float4 xw[128];                   // extra frames: mel taps owned by table row r: {w0, w1} of up to two mels with k0 = bin(r)
 };
 
 // tcgen05.mma, A operand in tensor memory; the shared-memory descriptor of B is passed as two words
@@ -83,6 +81,11 @@ __device__ __forceinline__ void t_umma_ts(uint32_t d_tmem, uint32_t a_tmem, uint
       :
       : "r"(d_tmem), "r"(a_tmem), "r"(b_lo), "r"(b_hi), "r"(kTIdesc), "r"(acc)
       : "memory");
+}
+__device__ __forceinline__ long long t_globaltimer() {
+  long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
 }
 __device__ __forceinline__ bool t_elect_one() {
   uint32_t pred;
@@ -142,6 +145,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTThreads, 1) melspe
   float* ybuf = reinterpret_cast<float*>(tab + 4 * kCTabBytes);        // kTYFloats
   float* stage = ybuf + 2 * kTYFloats;                                 // 2 x kCStageFloats (ybuf is double buffered)
   unsigned char* xt = reinterpret_cast<unsigned char*>(stage + 2 * kCStageFloats);   // [j & 1]{Exh | Oxh}
+  unsigned char* xtab = xt + 4 * kTXTileBytes;   // extra frames: {cos hi | sin hi} with row r = bin r - r / 32 (128 rows each)
   __shared__ TsShared sh;
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -155,7 +159,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTThreads, 1) melspe
 #define TL(slot)                                                                                             \
   do {                                                                                                       \
     if (kTimeline && blockIdx.x < 2 && lane == 0 && j >= a.tl_j0 && j < a.tl_j0 + kTlTilesT)                 \
-      a.tl[((blockIdx.x * kTlTilesT + (j - a.tl_j0)) * kTlSlotsT) + (slot)] = clock64();                     \
+      a.tl[((blockIdx.x * kTlTilesT + (j - a.tl_j0)) * kTlSlotsT) + (slot)] = t_globaltimer();                                  \
   } while (0)
 
   const uint32_t load_bar = c_smem_u32(&sh.load_bar), stage_free = c_smem_u32(&sh.stage_free);
@@ -189,10 +193,29 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTThreads, 1) melspe
     for (int i = tid; i < 2 * kTYFloats / 4; i += blockDim.x) yz[i] = make_float4(0.f, 0.f, 0.f, 0.f);
     uint4* xz = reinterpret_cast<uint4*>(xt);
     for (int i = tid; i < 4 * kTXTileBytes / 16; i += blockDim.x) xz[i] = make_uint4(0u, 0u, 0u, 0u);
-    for (int i = tid; i < a.n_mels; i += blockDim.x) {
-      sh.mel_k0[i] = a.mel_k0[i];
-      sh.mel_w0[i] = a.mel_w0[i];
-      sh.mel_w1[i] = a.mel_w1[i];
+    // Extra-frame operand: the hi tables again with every 32nd row repeating the next warp's first
+    // bin (row r holds bin r - r / 32), so that a lane finds its right neighbour's power with one
+    // shuffle and no warp needs another warp's lanes.  xw[r]: the taps of the (at most two) mels
+    // whose first bin is bin(r); rows 31, 63, 95, 127 only lend their value to lane 30.
+    for (int i = tid; i < 2 * 128 * 8; i += blockDim.x) {
+      const int t = i >> 10, r = (i >> 3) & 127, k8 = i & 7, b = r - (r >> 5);
+      const uint4 v = b < kCBins ? *reinterpret_cast<const uint4*>(a.tab + (size_t)(2 * t) * (kCTabBytes / 2) + c_umma_offset(b, 8 * k8) / 2)
+                                 : make_uint4(0u, 0u, 0u, 0u);
+      *reinterpret_cast<uint4*>(xtab + t * 16384 + c_umma_offset(r, 8 * k8)) = v;
+    }
+    if (tid < 128) {
+      const int b = tid - (tid >> 5);
+      float4 w = make_float4(0.f, 0.f, 0.f, 0.f);
+      if ((tid & 31) != 31) {
+        int found = 0;
+        for (int m = 0; m < a.n_mels; ++m)
+          if (a.mel_k0[m] == b) {
+            if (found == 0) { w.x = a.mel_w0[m]; w.y = a.mel_w1[m]; }
+            else { w.z = a.mel_w0[m]; w.w = a.mel_w1[m]; }
+            ++found;
+          }
+      }
+      sh.xw[tid] = w;
     }
   }
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -226,7 +249,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTThreads, 1) melspe
       // Every operand of the 24 MMAs of a tile is loop invariant except the accumulator buffer:
       // ring slot and barrier parities depend on the K-step only (4 steps per tile), the table
       // descriptors differ in their low word (14-bit address field) only.
-      const uint32_t tab0 = c_smem_u32(tab), xt0 = c_smem_u32(xt);
+      const uint32_t tab0 = c_smem_u32(tab), xt0 = c_smem_u32(xt), xtab0 = c_smem_u32(xtab);
       const uint32_t desc_hi = (uint32_t)(c_umma_desc(0) >> 32), lo_base = (uint32_t)c_umma_desc(0);
       auto dlo = [&](uint32_t addr) { return lo_base | ((addr >> 4) & 0x3FFFu); };
       uint32_t tlo[4][kFold / 16];   // [Ch, Cl, Sh, Sl][K-step]
@@ -265,9 +288,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTThreads, 1) melspe
                 const uint32_t xb = xt0 + (j & 1) * 2 * kTXTileBytes;
 #pragma unroll
                 for (int k2 = 0; k2 < kFold / 16; ++k2) {
-                  c_umma(dx, ((uint64_t)desc_hi << 32) | tlo[0][k2], ((uint64_t)desc_hi << 32) | dlo(xb + k2 * 256), k2 > 0,
-                         kTIdescX);
-                  c_umma(dx + kTXN, ((uint64_t)desc_hi << 32) | tlo[2][k2],
+                  c_umma(dx, ((uint64_t)desc_hi << 32) | dlo(xtab0 + k2 * 256), ((uint64_t)desc_hi << 32) | dlo(xb + k2 * 256),
+                         k2 > 0, kTIdescX);
+                  c_umma(dx + kTXN, ((uint64_t)desc_hi << 32) | dlo(xtab0 + 16384 + k2 * 256),
                          ((uint64_t)desc_hi << 32) | dlo(xb + kTXTileBytes + k2 * 256), k2 > 0, kTIdescX);
                 }
               }
@@ -596,6 +619,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTThreads, 1) melspe
       CH_PARK(kTMels / 8 - 1)
       c_tmem_wait_st();
       if (warp == 0) TL(12);
+      if (warp == kTEpiWarps - 1) TL(14);
 #undef CH_PART
 #undef CH_LOAD
 #undef CH_POW
@@ -604,20 +628,19 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTThreads, 1) melspe
 #undef CH_MEL1
 #undef CH_MEL2
 
-      // extra frames: lane = bin slot, column = frame; power -> shared -> mel maximum (warps 0-3)
+      // extra frames: lane = table row (bin r - r / 32), column = frame; the right neighbour's power
+      // comes from one shuffle, the taps from xw: no shared-memory round trip, no barrier (warps 0-3)
       if (n_extra > 0 && part == 0) {
         const uint32_t xaddr = tmem_base + ((uint32_t)(32 * warp) << 16) + kTXCol + (j & 1) * 2 * kTXN;
         float xr[4], xi[4];
         c_tmem_ld4(xaddr, xr);
         c_tmem_ld4(xaddr + kTXN, xi);
-        float* px = sh.px[j & 1];
+        const float4 w = sh.xw[tid];
 #pragma unroll
-        for (int x = 0; x < kCMaxExtra; ++x) px[x * 128 + tid] = fmaf(xr[x], xr[x], xi[x] * xi[x]);
-        c_named_bar(2, 128);
-        for (int i = tid; i < n_extra * a.n_mels; i += 128) {
-          const int x = i / a.n_mels, m = i - x * a.n_mels;
-          const int k0 = sh.mel_k0[m];
-          vmax = fmaxf(vmax, fmaf(sh.mel_w1[m], px[x * 128 + k0 + 1], sh.mel_w0[m] * px[x * 128 + k0]));
+        for (int x = 0; x < kCMaxExtra; ++x) {   // unused frames are zero rows of the operand: power 0
+          const float pw = fmaf(xr[x], xr[x], xi[x] * xi[x]);
+          const float pn = __shfl_down_sync(0xffffffffu, pw, 1);
+          vmax = fmaxf(vmax, fmaxf(fmaf(w.y, pn, w.x * pw), fmaf(w.w, pn, w.z * pw)));
         }
       }
       vmax = warp_max_nan(vmax);
@@ -639,6 +662,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTThreads, 1) melspe
       }
       __syncwarp();
       if (warp == 0) TL(13);
+      if (warp == kTEpiWarps - 1) TL(15);
       e_prev = e_j;
       // transposition schedule: record number q (of this cluster) is completely stashed by the
       // end of tile 16 q + 15; its group g is handled in tile 16 (q + 1) + 2 g + 1
@@ -677,7 +701,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTThreads, 1) melspe
 
 // ------------------------------------------------------------------------------------- host
 size_t melspec_ts_smem_bytes() {
-  return 4 * (size_t)kCTabBytes + sizeof(float) * (2 * (size_t)kTYFloats + 2 * (size_t)kCStageFloats) + 4 * (size_t)kTXTileBytes;
+  return 4 * (size_t)kCTabBytes + sizeof(float) * (2 * (size_t)kTYFloats + 2 * (size_t)kCStageFloats) + 4 * (size_t)kTXTileBytes +
+         2 * 16384;   // remapped hi tables of the extra frames
 }
 
 // Launches the TS kernel on `clusters` clusters of two CTAs; `a.n_items` must be the number of
@@ -698,7 +723,8 @@ int melspec_ts_run(const ChainArgs& a, long long clusters, cudaStream_t st) {
     configured[dev] = true;
   }
   // EEGSPEC_TIMELINE=<file>: debug only -- synchronous launch that dumps clock stamps of the
-  // pipeline hand-offs of CTAs 0 and 1 (64 tiles from EEGSPEC_TIMELINE_J0) as raw int64.
+  // pipeline hand-offs of CTAs 0 and 1 (64 tiles from EEGSPEC_TIMELINE_J0) as raw int64
+  // (%globaltimer nanoseconds, comparable between the two CTAs).
   const char* tl_path = getenv("EEGSPEC_TIMELINE");
   ChainArgs b = a;
   const size_t tl_bytes = sizeof(long long) * 2 * kTlTilesT * kTlSlotsT;

@@ -1,7 +1,7 @@
 """Debug timeline of the role-split mode-N kernel (run on the GPU box).
 
 EEGSPEC_TIMELINE makes the launch dump clock64 stamps of the pipeline hand-offs of CTAs 0 and 1;
-this prints, per tile, every stamp relative to the tile's MMA completion as seen by the epilogue.
+this prints, per tile, every stamp (nanoseconds of %globaltimer) relative to the tile's MMA completion as seen by the epilogue.
 """
 import os, sys
 import numpy as np, torch
@@ -20,14 +20,14 @@ torch.cuda.synchronize()
 tl = np.fromfile("/tmp/tl.bin", dtype=np.int64).reshape(2, 64, 32)
 names = {0: "b.top", 1: "b.loaded", 2: "b.diffed", 3: "b.tilesfree", 4: "b.built", 5: "m.ops", 6: "m.tmemfree",
          7: "m.issued", 8: "e.mmadone", 9: "e.xch", 10: "e.folded", 11: "e.flushed", 12: "e.main", 13: "e.arrived",
-         14: "p.epidone", 15: "p.published"}
+         14: "w15.main", 15: "w15.arrived"}
 if os.environ.get("TL_FINE"):
     names = {5: "m.ops0", 6: "m.tmemfree", 28: "m.iss0", 25: "m.ops1", 29: "m.iss1", 16: "b2.comp", 17: "b2.free", 18: "b2.st",
              19: "b2.arr", 26: "m.ops2", 30: "m.iss2", 20: "b3.comp", 21: "b3.free", 22: "b3.st", 23: "b3.arr", 27: "m.ops3",
              31: "m.iss3", 8: "e.mmadone"}
 for cta in range(2):
     t = tl[cta]
-    print(f"CTA {cta}: period (e.mmadone j+1 - j): mean {np.diff(t[8:56, 8]).mean():.0f} cycles")
+    print(f"CTA {cta}: period (e.mmadone j+1 - j): mean {np.diff(t[8:56, 8]).mean():.0f} ns")
     print("tile " + " ".join(f"{names[s]:>11s}" for s in names))
     for j in range(8, 24):
         base = t[j, 8]
