@@ -71,3 +71,57 @@ def test_errors():
         b200spec.EEGTransformer(n_feats=8, apply_chris_magic_ch8=True).transform(torch.zeros(500, 8, device="cuda"))
     with pytest.raises(NotImplementedError):
         b200spec.EEGTransformer(n_feats=19, downsample=16).transform(torch.zeros(1000, 20, device="cuda"))
+
+
+def test_span_cuts_do_not_change_a_bit(monkeypatch):
+    """The default configuration runs the span kernel, which cuts a record into spans to fill whole
+    waves (the cut depends on the batch size).  The state at a chunk start is rebuilt from the
+    zero-state ends of the three chunks before it, warm-up chunks included, so a cut record equals
+    an uncut one bit for bit; the per-record block-scan kernel (exact carry) agrees to rounding."""
+    rng = np.random.default_rng(33)
+    x = (np.cumsum(rng.standard_normal((5, 10000, 20)), 1) + rng.standard_normal((5, 10000, 20)) * 30).astype(np.float32)
+    x[1, 4000:4100, 3] = np.nan
+    x[2, :, 7] = 5000.0                                   # clipped to 1024
+    xt = torch.from_numpy(x).cuda()
+    for kw in (dict(n_feats=19, downsample=5), dict(n_feats=19, downsample=5, channel_major=True)):
+        t = b200spec.EEGTransformer(**kw)
+        cut = t.transform(xt)
+        monkeypatch.setenv("EEGSPEC_XF_ONE_SPAN", "1")
+        assert torch.equal(cut, t.transform(xt))
+        monkeypatch.delenv("EEGSPEC_XF_ONE_SPAN")
+        monkeypatch.setenv("EEGSPEC_XF_RECORD_KERNEL", "1")
+        scan = t.transform(xt)
+        monkeypatch.delenv("EEGSPEC_XF_RECORD_KERNEL")
+        assert (cut - scan).abs().max().item() <= 1e-4   # fp32 recurrences in a different order, values up to 32
+    x8 = np.ascontiguousarray(x[:, :, :8])
+    t8 = b200spec.EEGTransformer(n_feats=8, apply_chris_magic_ch8=True, downsample=5)
+    got = t8.transform(x8)
+    want = eo.eeg_transform_batch_oracle(x8, n_feats=8, apply_chris_magic_ch8=True, downsample=5)
+    assert np.abs(got - want).max() <= ATOL
+
+
+@pytest.mark.parametrize("length", [40, 1234, 9999, 10003])
+def test_ragged_lengths(length):
+    rng = np.random.default_rng(length)
+    x = (rng.standard_normal((3, length, 20)) * 40).astype(np.float32)
+    got = b200spec.EEGTransformer(n_feats=19, downsample=5).transform(x)
+    want = eo.eeg_transform_batch_oracle(x, n_feats=19, downsample=5)
+    assert got.shape == want.shape and np.abs(got - want).max() <= ATOL
+
+
+def test_slowly_decaying_filter_takes_the_exact_scan():
+    """Poles at radius 0.995: what a chunk leaves behind does not die within three chunks, so the
+    launch must pick the block-scan kernel (exact carry) instead of the truncating span kernel."""
+    from scipy.signal import lfilter
+    r, th = 0.995, 0.3
+    sec = np.array([1.0, -2 * r * np.cos(th), r * r])
+    a = np.convolve(sec, sec)
+    b = np.array([1e-4, 0, 0, 0, 0])
+    rng = np.random.default_rng(34)
+    x = (rng.standard_normal((2, 10000, 20)) * 40).astype(np.float32)
+    t = b200spec.EEGTransformer(n_feats=19, downsample=5)
+    for i in range(5):
+        t.params.b[i], t.params.a[i] = b[i], a[i]
+    got = t.transform(x)
+    want = lfilter(b, a, np.clip(x[:, :, :19], -1024, 1024) / 32.0, axis=1)[:, ::5]
+    assert np.abs(got - want).max() <= 2e-3 * max(1.0, np.abs(want).max())
