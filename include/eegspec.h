@@ -140,6 +140,12 @@ int eegspec_stft_image_host_f32(const float *x, int64_t rows, int64_t length, in
 int eegspec_melspec_host_f32(const float *eeg, int64_t batch, int32_t n_ch, int64_t length,
                              const eegspec_mel_params *p, float *out, int device);
 
+/* Bytes eegspec_melspec_host_f32 moves over PCIe for these arguments.  Channel-major records are
+ * copied row-wise: only the electrode rows some pair of the montage reads travel (16 of the 20
+ * EEG_COLUMNS rows for the HMS montage), the others are never touched on either side. */
+int eegspec_melspec_host_bytes(int64_t batch, int32_t n_ch, int64_t length, const eegspec_mel_params *p,
+                               int64_t *h2d_bytes, int64_t *d2h_bytes);
+
 /* ------------------------------------------------------------------------------------------
  * Row (f)1 -- the step in front of the path: raw-EEG transformer
  *   replaces _EEGTransformer.transform, /root/reference/root/src/data/dataset.py:73-104

@@ -57,6 +57,28 @@ static int pipe_open(int device, HostPipe** out) {
   return EEGSPEC_OK;
 }
 
+// Channel-major records: the rows of the electrodes some pair of the montage reads, as runs of
+// consecutive rows (HMS montage over EEG_COLUMNS: rows 0-7 and 11-18 of 20; Fz, Cz, Pz and EKG are
+// never read).  Returns 0 runs when every row is used or the record is time-major (one flat copy).
+static int used_channel_runs(const eegspec_mel_params* p, int n_ch, int* start, int* len) {
+  if (p->time_major || n_ch > 256) return 0;
+  bool used[256] = {};
+  const int n_pairs = p->n_chains * p->pairs_per_chain;
+  for (int i = 0; i < n_pairs && i < EEGSPEC_MAX_PAIRS; ++i) {
+    if (p->pair_a[i] < 0 || p->pair_a[i] >= n_ch || p->pair_b[i] < 0 || p->pair_b[i] >= n_ch) return 0;
+    used[p->pair_a[i]] = used[p->pair_b[i]] = true;
+  }
+  int n = 0, n_used = 0;
+  for (int c = 0; c < n_ch; ++c) {
+    if (!used[c]) continue;
+    ++n_used;
+    if (n && start[n - 1] + len[n - 1] == c) ++len[n - 1];
+    else if (n == EEGSPEC_MAX_PAIRS) return 0;
+    else { start[n] = c; len[n] = 1; ++n; }
+  }
+  return n_used == n_ch ? 0 : n;
+}
+
 }  // namespace eegspec
 
 using namespace eegspec;
@@ -214,6 +236,8 @@ int eegspec_melspec_host_f32(const float* eeg, int64_t batch, int32_t n_ch, int6
   int64_t chunk = 64;
   if (chunk > batch) chunk = batch;
   const size_t ws_bytes = melspec_workspace(chunk, p);
+  int run_start[EEGSPEC_MAX_PAIRS], run_len[EEGSPEC_MAX_PAIRS];
+  const int n_runs = used_channel_runs(p, n_ch, run_start, run_len);
 
   int n = 0;
   for (int64_t r0 = 0; r0 < batch; r0 += chunk, ++n) {
@@ -224,9 +248,17 @@ int eegspec_melspec_host_f32(const float* eeg, int64_t batch, int32_t n_ch, int6
     if ((e = pipe_reserve(*pipe, s, 1, out_rec * chunk)) != cudaSuccess) return (int)e;
     if ((e = pipe_reserve(*pipe, s, 2, ws_bytes)) != cudaSuccess) return (int)e;
     cudaStream_t st = pipe->stream[s];
-    e = cudaMemcpyAsync(pipe->buf[s][0], eeg + r0 * (int64_t)n_ch * length, in_rec * nb,
-                        cudaMemcpyHostToDevice, st);
-    if (e != cudaSuccess) return (int)e;
+    if (n_runs == 0) {
+      e = cudaMemcpyAsync(pipe->buf[s][0], eeg + r0 * (int64_t)n_ch * length, in_rec * nb,
+                          cudaMemcpyHostToDevice, st);
+      if (e != cudaSuccess) return (int)e;
+    }
+    for (int r = 0; r < n_runs; ++r) {   // only the electrode rows the montage reads: same layout, gaps left stale
+      e = cudaMemcpy2DAsync(static_cast<float*>(pipe->buf[s][0]) + (int64_t)run_start[r] * length, in_rec,
+                            eeg + (r0 * (int64_t)n_ch + run_start[r]) * length, in_rec,
+                            (size_t)run_len[r] * length * sizeof(float), (size_t)nb, cudaMemcpyHostToDevice, st);
+      if (e != cudaSuccess) return (int)e;
+    }
     rc = melspec_launch(static_cast<const float*>(pipe->buf[s][0]), nb, n_ch, length,
                         (long long)n_ch * length, p, static_cast<float*>(pipe->buf[s][1]),
                         pipe->buf[s][2], pipe->cap[s][2], st);
@@ -239,6 +271,21 @@ int eegspec_melspec_host_f32(const float* eeg, int64_t batch, int32_t n_ch, int6
     cudaError_t e = cudaStreamSynchronize(pipe->stream[s]);
     if (e != cudaSuccess) return (int)e;
   }
+  return EEGSPEC_OK;
+}
+
+int eegspec_melspec_host_bytes(int64_t batch, int32_t n_ch, int64_t length, const eegspec_mel_params* p,
+                               int64_t* h2d_bytes, int64_t* d2h_bytes) {
+  if (!p || batch < 0 || n_ch <= 0 || length <= 0) return EEGSPEC_EINVAL;
+  MelGeometry g;
+  const int rc = melspec_geometry(p, &g);
+  if (rc != EEGSPEC_OK) return rc;
+  int run_start[EEGSPEC_MAX_PAIRS], run_len[EEGSPEC_MAX_PAIRS];
+  const int n_runs = used_channel_runs(p, n_ch, run_start, run_len);
+  int64_t rows = n_runs ? 0 : n_ch;
+  for (int r = 0; r < n_runs; ++r) rows += run_len[r];
+  if (h2d_bytes) *h2d_bytes = batch * rows * length * (int64_t)sizeof(float);
+  if (d2h_bytes) *d2h_bytes = batch * (int64_t)p->n_mels * g.n_time * p->n_chains * (int64_t)sizeof(float);
   return EEGSPEC_OK;
 }
 

@@ -134,6 +134,19 @@ def test_host_front_door_and_determinism():
     dev = b200spec.eeg_to_spectrogram(x.cuda())
     assert torch.equal(out, dev.cpu())
     assert torch.equal(dev, b200spec.eeg_to_spectrogram(x.cuda()))
+    # the host call copies only the electrode rows the montage reads (0-7 and 11-18 of EEG_COLUMNS):
+    # Fz, Cz, Pz and EKG never travel, so poisoning them changes nothing
+    y = x.clone()
+    y[:, [8, 9, 10, 19]] = float("nan")
+    assert torch.equal(out, b200spec.eeg_to_spectrogram(y.pin_memory()))
+    import ctypes
+    from b200spec import _native as nat
+    h2d, d2h = ctypes.c_int64(), ctypes.c_int64()
+    p = b200spec.mel_params()
+    nat.check(nat.lib.eegspec_melspec_host_bytes(130, 20, 10000, ctypes.byref(p), ctypes.byref(h2d), ctypes.byref(d2h)), "bytes")
+    assert h2d.value == 130 * 16 * 10000 * 4 and d2h.value == out.numel() * 4
+    tm = b200spec.eeg_to_spectrogram(x[:3].transpose(1, 2).contiguous(), time_major=True)   # parquet layout: one flat copy
+    assert (tm - out[:3]).abs().max().item() <= ATOL          # another engine reads time-major records
 
 
 def test_errors():
