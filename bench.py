@@ -22,9 +22,9 @@ import sys
 import threading
 import time
 
-# rank 0 prints ONE JSON line on stdout: keep NCCL's version banner (NCCL_DEBUG=VERSION) off it
-if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
-    os.environ["NCCL_DEBUG"] = "WARN"
+# rank 0 prints ONE JSON line on stdout: NCCL logs (its version banner included) go to stdout by
+# default, so send them to stderr whatever NCCL_DEBUG level the launcher chose
+os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:

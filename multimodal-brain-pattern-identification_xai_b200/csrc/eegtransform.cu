@@ -352,6 +352,164 @@ __global__ void __launch_bounds__(32 * kSpChunks) eeg_transform_span_kernel(cons
   }
 }
 
+// ------------------------------------------------------- span kernel, one warp per 4 channels
+// Same arithmetic and the same cut into spans as the kernel above; the difference is who talks to
+// whom.  A warp owns FOUR output channels for the whole span: lane = (chunk k' of the tile's 8,
+// channel cc of the warp's 4).  The three previous chunks a lane needs live in the SAME warp (the
+// lanes 4, 8 and 12 below it, or the warp's own registers of the previous tile), so the chunk
+// states travel by shuffle: no shared-memory state ring and no CTA barrier in the loop.  Warps
+// only meet at the tile pipeline: a `full` mbarrier per stage (TMA bytes) and an `empty` one
+// (one arrival per warp) before a stage is refilled.  Chunk rows are padded to a stride of
+// 4 mod 32 banks: bank = 4 k' + channel, conflict-free for a channel selection of consecutive rows.
+constexpr int kLnChunks = 8;                        // chunks per tile = lanes / 4
+constexpr int kLnTile = kSpChunk * kLnChunks;       // 320 samples
+
+template <int NC, bool DIFF>
+__global__ void __launch_bounds__(256) eeg_transform_lane_kernel(const SpArgs a) {
+  extern __shared__ __align__(128) float xs[];      // [2][kLnChunks][stride]
+  __shared__ __align__(8) uint64_t bars[4];         // full[2], empty[2]
+
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, n_warps = blockDim.x >> 5;
+  const int k = lane >> 2, c = warp * 4 + (lane & 3);
+  const bool live = c < a.n_out;
+  const int ca = live ? a.sel_a[c] : 0, cb = (DIFF && live) ? a.sel_b[c] : 0;
+  const int rec = blockIdx.x / a.units;
+  const int unit = blockIdx.x - rec * a.units;
+  const float* xr = a.x + (long long)rec * a.rec_stride;
+  const int length = (int)a.length;
+  const int span_start = unit * a.span;
+  const int span_end = min(length, span_start + a.span);
+  const int t_begin = span_start - (unit ? kSpWarm * kSpChunk : 0);
+  const int n_tiles = (span_end - t_begin + kLnTile - 1) / kLnTile;
+  const uint32_t xs_u32 = c_smem_u32(xs), full0 = c_smem_u32(&bars[0]), empty0 = c_smem_u32(&bars[2]);
+  const int buf_floats = kLnChunks * a.stride;
+
+  if (tid == 0) {
+    c_mbar_init(full0, 1);
+    c_mbar_init(full0 + 8, 1);
+    c_mbar_init(empty0, n_warps);
+    c_mbar_init(empty0 + 8, n_warps);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+
+  auto issue = [&](int tile) {   // one thread: the valid rows of each chunk, one bulk copy per chunk
+    const int t0 = t_begin + tile * kLnTile;
+    const uint32_t bar = full0 + 8u * (tile & 1);
+    const uint32_t dst = xs_u32 + 4u * (uint32_t)((tile & 1) * buf_floats);
+    int rows_total = min(kLnTile, span_end - t0);
+    c_mbar_expect_tx(bar, (uint32_t)rows_total * NC * 4u);
+    for (int kk = 0; kk < kLnChunks && rows_total > 0; ++kk, rows_total -= kSpChunk) {
+      const int rows = min(rows_total, kSpChunk);
+      c_bulk_g2s(dst + 4u * (uint32_t)(kk * a.stride), xr + (long long)(t0 + kk * kSpChunk) * NC,
+                 (uint32_t)rows * NC * 4u, bar);
+    }
+  };
+  if (tid == 0) issue(0);
+
+  const float b0 = a.b[0], b1 = a.b[1], b2 = a.b[2], b3 = a.b[3], b4 = a.b[4];
+  const float na1 = -a.a[1], na2 = -a.a[2], na3 = -a.a[3], na4 = -a.a[4];
+  const float clip = a.clip;
+  const int o_begin = span_start / kSpDs, o_end = (span_end + kSpDs - 1) / kSpDs;
+  const int l_out = (int)a.l_out;
+  float p0 = 0.f, p1 = 0.f, p2 = 0.f, p3 = 0.f;   // this lane's chunk state of the previous tile
+  const float* xbase = xs + k * a.stride;
+  int t_chunk = t_begin + k * kSpChunk;
+
+  for (int tile = 0; tile < n_tiles; ++tile, t_chunk += kLnTile) {
+    if (tid == 0 && tile + 1 < n_tiles) {
+      if (tile >= 1) c_mbar_wait(empty0 + 8u * ((tile + 1) & 1), ((tile - 1) >> 1) & 1);   // every warp left that stage
+      issue(tile + 1);
+    }
+    __syncwarp();
+    c_mbar_wait(full0 + 8u * (tile & 1), (tile >> 1) & 1);
+    const int rows = max(0, min(kSpChunk, span_end - t_chunk));
+    const float* xp = xbase + (tile & 1) * buf_floats;
+
+    float yz[kSpP];
+    float z0 = 0.f, z1 = 0.f, z2 = 0.f, z3 = 0.f;
+#define XF_STEP(n, keep)                                                   \
+  {                                                                        \
+    float v = xp[(n) * NC + ca];                                           \
+    if (DIFF) v -= xp[(n) * NC + cb];                                      \
+    v = (v != v) ? 0.f : fminf(fmaxf(v, -clip), clip);                     \
+    const float t0 = fmaf(b1, v, z1), t1 = fmaf(b2, v, z2), t2 = fmaf(b3, v, z3), t3 = b4 * v; \
+    const float y = fmaf(b0, v, z0);                                       \
+    z0 = fmaf(na1, y, t0);                                                 \
+    z1 = fmaf(na2, y, t1);                                                 \
+    z2 = fmaf(na3, y, t2);                                                 \
+    z3 = fmaf(na4, y, t3);                                                 \
+    if (keep) yz[(n) / kSpDs] = y;                                         \
+  }
+    if (__all_sync(0xffffffffu, rows == kSpChunk)) {
+#pragma unroll
+      for (int n = 0; n < kSpChunk; ++n) XF_STEP(n, (n % kSpDs) == 0)
+    } else {   // the span ends inside this tile: chunks past the end are never stored
+#pragma unroll
+      for (int m = 0; m < kSpP; ++m) {
+        yz[m] = 0.f;
+        for (int r = 0; r < kSpDs; ++r) {
+          const int n = m * kSpDs + r;
+          if (n < rows) XF_STEP(n, r == 0)
+        }
+      }
+    }
+#undef XF_STEP
+    __syncwarp();
+    if (lane == 0) c_mbar_arrive(empty0 + 8u * (tile & 1));   // this warp is done with the stage
+
+    // ---- start state of chunk k = z_{k-1} + M z_{k-2} + M^2 z_{k-3}, neighbours by shuffle
+    float f[EEGSPEC_XF_ORDER];
+    {
+      const int s1 = (lane - 4) & 31, s2 = (lane - 8) & 31, s3 = (lane - 12) & 31;
+      const float zc[4] = {z0, z1, z2, z3}, pc[4] = {p0, p1, p2, p3};
+      float q1[4], q2[4], q3[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float a1 = __shfl_sync(0xffffffffu, zc[i], s1), e1 = __shfl_sync(0xffffffffu, pc[i], s1);
+        const float a2 = __shfl_sync(0xffffffffu, zc[i], s2), e2 = __shfl_sync(0xffffffffu, pc[i], s2);
+        const float a3 = __shfl_sync(0xffffffffu, zc[i], s3), e3 = __shfl_sync(0xffffffffu, pc[i], s3);
+        q1[i] = k >= 1 ? a1 : e1;
+        q2[i] = k >= 2 ? a2 : e2;
+        q3[i] = k >= 3 ? a3 : e3;
+      }
+#pragma unroll
+      for (int i = 0; i < EEGSPEC_XF_ORDER; ++i)
+        f[i] = q1[i] + (a.m[i][0] * q2[0] + a.m[i][1] * q2[1] + a.m[i][2] * q2[2] + a.m[i][3] * q2[3]) +
+               (a.m2[i][0] * q3[0] + a.m2[i][1] * q3[1] + a.m2[i][2] * q3[2] + a.m2[i][3] * q3[3]);
+      p0 = z0; p1 = z1; p2 = z2; p3 = z3;
+    }
+#pragma unroll
+    for (int m = 0; m < kSpP; ++m)
+      yz[m] += a.g[0][m] * f[0] + a.g[1][m] * f[1] + a.g[2][m] * f[2] + a.g[3][m] * f[3];
+
+    if (live) {
+      const int o0 = t_chunk / kSpDs;
+      const bool whole = o0 >= o_begin && o0 + kSpP <= o_end;
+      if (a.out_channel_major) {
+        float* o = a.out + ((long long)rec * a.n_out + c) * l_out + o0;
+        if (whole && !((l_out | (int)(reinterpret_cast<uintptr_t>(a.out) >> 2)) & 3)) {   // one full sector per thread
+          reinterpret_cast<float4*>(o)[0] = make_float4(yz[0], yz[1], yz[2], yz[3]);
+          reinterpret_cast<float4*>(o)[1] = make_float4(yz[4], yz[5], yz[6], yz[7]);
+        } else {
+#pragma unroll
+          for (int m = 0; m < kSpP; ++m)
+            if (whole || (o0 + m >= o_begin && o0 + m < o_end)) o[m] = yz[m];
+        }
+      } else if (whole && a.n_out == 19) {   // constant offsets
+        float* o = a.out + ((long long)rec * l_out + o0) * 19 + c;
+#pragma unroll
+        for (int m = 0; m < kSpP; ++m) o[m * 19] = yz[m];
+      } else {
+        float* o = a.out + ((long long)rec * l_out + o0) * a.n_out + c;
+#pragma unroll
+        for (int m = 0; m < kSpP; ++m)
+          if (whole || (o0 + m >= o_begin && o0 + m < o_end)) o[m * a.n_out] = yz[m];
+      }
+    }
+  }
+}
+
 // ------------------------------------------------------------------------------------- host
 // Direct form II transposed, one step (double precision): the recurrence SciPy's lfilter runs.
 static double df2t_step(const double* b, const double* a, double* z, double v) {
@@ -429,11 +587,23 @@ static int span_launch(const float* x, long long batch, long long length, int n_
     for (int r = 0; r < EEGSPEC_XF_ORDER; ++r) decay = fmax(decay, fabs(z[r]));
   }
   if (!(decay < 1e-9)) return kSpanNotApplicable;   // a slowly decaying filter: the exact block scan above
-  a.stride = kSpChunk * n_ch + ((p->n_out + 3) & ~3);
-  const size_t smem = sizeof(float) * (2 * (size_t)kSpChunks * a.stride +
-                                       3 * (size_t)kSpChunks * EEGSPEC_XF_ORDER * ((p->n_out + 3) & ~3));
-  const int threads = (kSpChunks * p->n_out + 31) & ~31;
-  void (*kernel)(const SpArgs) = diff ? eeg_transform_span_kernel<8, true> : eeg_transform_span_kernel<20, false>;
+  const char* which = getenv("EEGSPEC_XF_KERNEL");
+  const bool lanes = !(which && !strcmp(which, "span")) && length < (1LL << 30);   // default: one warp per 4 channels
+  size_t smem;
+  int threads;
+  void (*kernel)(const SpArgs);
+  if (lanes) {
+    a.stride = kSpChunk * n_ch + 4;
+    smem = sizeof(float) * 2 * (size_t)kLnChunks * a.stride;
+    threads = 32 * ((p->n_out + 3) / 4);
+    kernel = diff ? eeg_transform_lane_kernel<8, true> : eeg_transform_lane_kernel<20, false>;
+  } else {
+    a.stride = kSpChunk * n_ch + ((p->n_out + 3) & ~3);
+    smem = sizeof(float) * (2 * (size_t)kSpChunks * a.stride +
+                            3 * (size_t)kSpChunks * EEGSPEC_XF_ORDER * ((p->n_out + 3) & ~3));
+    threads = (kSpChunks * p->n_out + 31) & ~31;
+    kernel = diff ? eeg_transform_span_kernel<8, true> : eeg_transform_span_kernel<20, false>;
+  }
   cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return (int)e;
   int dev = 0, sms = 0, occ = 0;

@@ -89,6 +89,9 @@ def test_span_cuts_do_not_change_a_bit(monkeypatch):
         monkeypatch.setenv("EEGSPEC_XF_ONE_SPAN", "1")
         assert torch.equal(cut, t.transform(xt))
         monkeypatch.delenv("EEGSPEC_XF_ONE_SPAN")
+        monkeypatch.setenv("EEGSPEC_XF_KERNEL", "span")     # the shared-memory state ring variant: same arithmetic
+        assert torch.equal(cut, t.transform(xt))
+        monkeypatch.delenv("EEGSPEC_XF_KERNEL")
         monkeypatch.setenv("EEGSPEC_XF_RECORD_KERNEL", "1")
         scan = t.transform(xt)
         monkeypatch.delenv("EEGSPEC_XF_RECORD_KERNEL")
