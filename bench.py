@@ -339,7 +339,7 @@ def main():
             "workload": "(1024,10000,20)->(1024,2000,19) per GPU, 819 MB in per step (> L2)",
             "value": world * RECORDS * args.steps / (ms_xf * 1e-3), "unit": UNIT, "ms_per_step": ms_xf / args.steps,
             "roofline": {"bound": "hbm", "achieved": a_xf, "peak": peak, "unit": "GB/s", "frac": a_xf / peak, "traffic": committed_traffic("eeg_transform_dram_bytes_per_launch"),
-                         "kernel": f"eeg_transform_span_kernel<20,0>, {bytes_xf} B/record"}}
+                         "kernel": f"eeg_transform_lane_kernel<20,0>, {bytes_xf} B/record"}}
 
     if "e2e" in legs:
         # ------------------------------------------------------------ end to end: host buffers in and out

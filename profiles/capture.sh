@@ -26,5 +26,5 @@ cap() {  # name regex skip
 cap melspec_ts melspec_ts_kernel 3
 cap stft_hms50s stft_image_kernel 3
 cap stft_diffeeg stft_image_kernel 8
-cap eeg_transform eeg_transform_span_kernel 3
+cap eeg_transform eeg_transform_lane_kernel 3
 ls -la $OUT
