@@ -364,6 +364,23 @@ __global__ void __launch_bounds__(32 * kSpChunks) eeg_transform_span_kernel(cons
 constexpr int kLnChunks = 8;                        // chunks per tile = lanes / 4
 constexpr int kLnTile = kSpChunk * kLnChunks;       // 320 samples
 
+// Wait for a tile with back-off: the data is microseconds away, and a tight try_wait loop was 10 %
+// of all instructions issued (it competes with the warps that have work).
+__device__ __forceinline__ void xf_mbar_wait_sleep(uint32_t bar, uint32_t parity) {
+  for (;;) {
+    uint32_t done;
+    asm volatile(
+        "{\n\t.reg .pred P1;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, P1;\n\t}\n"
+        : "=r"(done)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    if (done) break;
+    __nanosleep(128);
+  }
+}
+
 template <int NC, bool DIFF>
 __global__ void __launch_bounds__(256) eeg_transform_lane_kernel(const SpArgs a) {
   extern __shared__ __align__(128) float xs[];      // [2][kLnChunks][stride]
@@ -422,7 +439,7 @@ __global__ void __launch_bounds__(256) eeg_transform_lane_kernel(const SpArgs a)
       issue(tile + 1);
     }
     __syncwarp();
-    c_mbar_wait(full0 + 8u * (tile & 1), (tile >> 1) & 1);
+    xf_mbar_wait_sleep(full0 + 8u * (tile & 1), (tile >> 1) & 1);
     const int rows = max(0, min(kSpChunk, span_end - t_chunk));
     const float* xp = xbase + (tile & 1) * buf_floats;
 
