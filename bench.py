@@ -181,6 +181,10 @@ def main():
 
     assert torch.cuda.is_available(), "bench.py needs a GPU (there is no CPU path)"
     torch.cuda.set_device(local)
+    bound = []
+    if world > 1:   # one process per GPU: sit on the socket the GPU's PCIe link hangs off (host-buffer leg)
+        from b200spec.sharding import bind_host_to_gpu
+        bound = bind_host_to_gpu(local)
     dist = None
     if world > 1:
         import torch.distributed as dist
@@ -281,7 +285,8 @@ def main():
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": WORKLOAD_N, "mode": "N", "records_per_gpu": RECORDS,
                    "l2": "inputs are 819 MB per step per GPU (> 126 MB L2); no flush needed",
-                   "parallelism": f"records sharded over {world} GPU(s), no collective"},
+                   "parallelism": f"records sharded over {world} GPU(s), no collective",
+                   "host_cores_bound_rank0": len(bound)},
         "roofline": roofline, "gpu_launches": int(launches_total), "clocks": clocks,
     }
 

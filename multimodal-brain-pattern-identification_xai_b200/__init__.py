@@ -32,6 +32,7 @@ _API = {
     "shard_bounds": "sharding",
     "shard_slice": "sharding",
     "gather_spectrograms": "sharding",
+    "bind_host_to_gpu": "sharding",
     "EEG_COLUMNS": "montage",
     "MAP_FEATURES": "montage",
     "CHAIN_ORDER": "montage",

@@ -44,3 +44,36 @@ def gather_spectrograms(local: torch.Tensor, n_records: int, group=None) -> torc
     dist.all_gather_into_tensor(out, padded.contiguous(), group=group)
     parts = [out[r * biggest: r * biggest + (hi - lo)] for r, (lo, hi) in enumerate(sizes)]
     return torch.cat(parts, dim=0)
+
+
+def bind_host_to_gpu(device_index: int) -> list[int]:
+    """Pin this process to the CPU cores next to GPU ``device_index`` (its NUMA node), so that the
+    pinned host buffers it allocates afterwards (first touch) and the copy threads sit on the
+    socket the GPU's PCIe link hangs off.  One process per GPU: without it eight ranks share
+    whatever node the launcher started them on and the host-buffer path runs at a fraction of the
+    link rate.  Returns the cores bound to ([] when NVML or the affinity call is unavailable;
+    binding is an optimisation, never a requirement)."""
+    import os
+
+    try:
+        import pynvml
+
+        pynvml.nvmlInit()
+        visible = os.environ.get("CUDA_VISIBLE_DEVICES")
+        if visible:                                           # NVML enumerates physical devices
+            ids = [v.strip() for v in visible.split(",") if v.strip()]
+            tok = ids[device_index]
+            handle = pynvml.nvmlDeviceGetHandleByUUID(tok) if tok.startswith("GPU-") else \
+                pynvml.nvmlDeviceGetHandleByIndex(int(tok))
+        else:
+            handle = pynvml.nvmlDeviceGetHandleByIndex(device_index)
+        n_cpu = os.cpu_count() or 1
+        words = pynvml.nvmlDeviceGetCpuAffinity(handle, (n_cpu + 63) // 64)
+        allowed = os.sched_getaffinity(0)
+        cores = [c for c in range(n_cpu) if (words[c // 64] >> (c % 64)) & 1 and c in allowed]
+        if not cores:
+            return []
+        os.sched_setaffinity(0, cores)
+        return cores
+    except Exception:
+        return []

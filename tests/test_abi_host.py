@@ -86,6 +86,21 @@ def test_mel_defaults_and_geometry():
         b200spec.melspec_geometry(b200spec.mel_params(fmax=500.0))
 
 
+def test_host_door_byte_count():
+    """The mel host door copies in only the electrode rows some montage pair reads: 16 of the 20
+    EEG_COLUMNS rows (Fz, Cz, Pz and EKG stay home); a time-major record travels whole."""
+    p = b200spec.mel_params()
+    used = {p.pair_a[i] for i in range(16)} | {p.pair_b[i] for i in range(16)}
+    assert len(used) == 16 and not used & {8, 9, 10, 19}
+    h2d, d2h = C.c_int64(), C.c_int64()
+    assert nat.lib.eegspec_melspec_host_bytes(7, 20, 10000, C.byref(p), C.byref(h2d), C.byref(d2h)) == 0
+    assert (h2d.value, d2h.value) == (7 * 16 * 10000 * 4, 7 * 128 * 256 * 4 * 4)
+    tm = b200spec.mel_params(time_major=True)
+    assert nat.lib.eegspec_melspec_host_bytes(7, 20, 10000, C.byref(tm), C.byref(h2d), None) == 0
+    assert h2d.value == 7 * 20 * 10000 * 4
+    assert nat.lib.eegspec_melspec_host_bytes(7, 0, 10000, C.byref(p), C.byref(h2d), None) == nat.EINVAL
+
+
 def test_montage_constants_match_oracle():
     from b200spec import montage
 

@@ -42,3 +42,16 @@ def test_gather_restores_record_order_world2(n_records):
         s.bind(("127.0.0.1", 0))
         port = s.getsockname()[1]
     mp.spawn(_worker, args=(2, port, n_records), nprocs=2, join=True)
+
+
+def test_bind_host_to_gpu_is_optional():
+    """No NVML / no GPU here: the binding helper reports nothing bound and leaves the affinity alone."""
+    import os
+
+    from b200spec.sharding import bind_host_to_gpu
+
+    before = os.sched_getaffinity(0)
+    cores = bind_host_to_gpu(0)
+    assert isinstance(cores, list)
+    assert os.sched_getaffinity(0) == (set(cores) if cores else before)
+    os.sched_setaffinity(0, before)
