@@ -22,9 +22,25 @@ import sys
 import threading
 import time
 
-# rank 0 prints ONE JSON line on stdout: NCCL logs (its version banner included) go to stdout by
-# default, so send them to stderr whatever NCCL_DEBUG level the launcher chose
-os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+# rank 0 prints ONE JSON line on stdout.  Libraries write there too (NCCL's version banner is a
+# C-level printf on fd 1 and ignores NCCL_DEBUG_FILE), so keep a private handle on the real stdout
+# for the JSON line and point fd 1 at stderr for everything else.
+_JSON_OUT = None
+
+
+def claim_stdout():
+    global _JSON_OUT
+    if _JSON_OUT is None:
+        sys.stdout.flush()
+        _JSON_OUT = os.fdopen(os.dup(1), "w")
+        os.dup2(2, 1)
+
+
+def emit(obj):
+    claim_stdout()
+    _JSON_OUT.write(json.dumps(obj) + "\n")
+    _JSON_OUT.flush()
+
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
@@ -150,10 +166,11 @@ def reference_arm(args, rank, world):
                    "sample": f"{r['records']} records"},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def main():
+    claim_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
@@ -417,7 +434,7 @@ def main():
                             "sample": f"{c_r['records']} records (19,2000) through compute_stft_port", "per_core": c_r["per_core_records_per_s"]},
                 "hms50s": {"value": c_r50["records_per_s"], "unit": UNIT, "cores": arm.cores, "kind": "port",
                            "sample": f"{c_r50['records']} records (20,10000) through compute_stft_port", "per_core": c_r50["per_core_records_per_s"]}}
-        print(json.dumps(result), flush=True)
+        emit(result)
     if dist is not None:
         dist.destroy_process_group()
 
