@@ -460,6 +460,72 @@ static int device_tables(const eegspec_mel_params& p, MelTables* out, MelGeometr
 
 constexpr long long kMelChunk = 256;  // records per scratch pass
 
+// ---------------------------------------------------------------- time-major records (parquet layout)
+// The reference reads records as (L, 20) rows of a parquet frame.  Engine 3 wants electrode rows
+// (TMA row copies), so a time-major batch first goes through this gather: the crop window of the
+// electrodes some pair reads, as compact channel-major rows in the workspace.  One tile of 256
+// samples x n_ch per CTA through shared memory (row pitch n_ch + 1: a warp reading one electrode of
+// 32 consecutive samples touches 32 banks); loads and stores are full 128-byte lines.
+constexpr int kGatherTile = 256;
+struct GatherRows { int n, r[2 * EEGSPEC_MAX_PAIRS]; };
+
+__global__ void __launch_bounds__(kGatherTile) gather_rows_kernel(const float* __restrict__ x, long long rec_stride,
+                                                                  int n_ch, int t0, int crop, const GatherRows rows,
+                                                                  float* __restrict__ out) {
+  extern __shared__ float tile[];   // [kGatherTile][n_ch + 1]
+  const int tid = threadIdx.x, s0 = blockIdx.x * kGatherTile;
+  const long long rec = blockIdx.y;
+  const int n_valid = min(kGatherTile, crop - s0);
+  const float* src = x + rec * rec_stride + (long long)(t0 + s0) * n_ch;
+  const int n_el = n_valid * n_ch, pitch = n_ch + 1;
+  if (!(n_ch & 3) && !(reinterpret_cast<uintptr_t>(src) & 15)) {
+    for (int e = 4 * tid; e < n_el; e += 4 * kGatherTile) {
+      const float4 v = __ldg(reinterpret_cast<const float4*>(src + e));
+      const int s = e / n_ch, c = e - s * n_ch;   // the four stay in one sample row (n_ch % 4 == 0)
+      float* d = tile + s * pitch + c;
+      d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
+    }
+  } else {
+    for (int e = tid; e < n_el; e += kGatherTile) {
+      const int s = e / n_ch;
+      tile[s * pitch + (e - s * n_ch)] = __ldg(src + e);
+    }
+  }
+  __syncthreads();
+  if (tid < n_valid) {
+    float* o = out + rec * (long long)rows.n * crop + s0 + tid;
+    for (int u = 0; u < rows.n; ++u) o[(long long)u * crop] = tile[tid * pitch + rows.r[u]];
+  }
+}
+
+// Distinct electrodes of the montage in ascending order; pair indices rewritten to positions in it.
+static int compact_rows(const eegspec_mel_params& p, int* rows, int* pair_a, int* pair_b) {
+  const int n_pairs = p.n_chains * p.pairs_per_chain;
+  int n = 0;
+  for (int pass = 0; pass < 2; ++pass)
+    for (int i = 0; i < n_pairs; ++i) {
+      const int c = pass ? p.pair_b[i] : p.pair_a[i];
+      bool seen = false;
+      for (int j = 0; j < n; ++j) seen |= rows[j] == c;
+      if (!seen) rows[n++] = c;
+    }
+  for (int i = 1; i < n; ++i)   // insertion sort: <= 64 entries
+    for (int j = i; j > 0 && rows[j - 1] > rows[j]; --j) { const int t = rows[j]; rows[j] = rows[j - 1]; rows[j - 1] = t; }
+  for (int i = 0; i < n_pairs; ++i)
+    for (int j = 0; j < n; ++j) {
+      if (rows[j] == p.pair_a[i]) pair_a[i] = j;
+      if (rows[j] == p.pair_b[i]) pair_b[i] = j;
+    }
+  return n;
+}
+
+constexpr long long kGatherChunk = 1024;   // records per gather + engine-3 pass
+
+static size_t gather_scratch_per_record(const eegspec_mel_params& p) {
+  int rows[2 * EEGSPEC_MAX_PAIRS], pa[EEGSPEC_MAX_PAIRS], pb[EEGSPEC_MAX_PAIRS];
+  return (size_t)compact_rows(p, rows, pa, pb) * (size_t)p.crop * sizeof(float);
+}
+
 static size_t per_record_scratch(const eegspec_mel_params& p, const MelGeometry& g) {
   const size_t q = (size_t)g.n_pairs * p.n_mels * g.n_time * sizeof(float);
   const size_t r = (size_t)g.n_pairs * sizeof(float);
@@ -470,7 +536,12 @@ size_t melspec_workspace(long long batch, const eegspec_mel_params* p) {
   MelGeometry g;
   if (batch <= 0 || melspec_geometry(p, &g) != EEGSPEC_OK) return 0;
   const long long chunk = batch < kMelChunk ? batch : kMelChunk;
-  return per_record_scratch(*p, g) * (size_t)chunk;
+  size_t need = per_record_scratch(*p, g) * (size_t)chunk;
+  if (p->time_major) {   // room for the gathered electrode rows of one engine-3 pass (+ the row list)
+    const size_t tm = gather_scratch_per_record(*p) * (size_t)(batch < kGatherChunk ? batch : kGatherChunk);
+    if (tm > need) need = tm;
+  }
+  return need;
 }
 
 static size_t pair_kernel_smem(const eegspec_mel_params& p) {
@@ -521,6 +592,45 @@ int melspec_launch(const float* eeg, long long batch, int n_ch, long long length
   for (int i = 0; i < EEGSPEC_MAX_PAIRS; ++i) {
     a.pair_a[i] = i < n_pairs ? p->pair_a[i] : 0;
     a.pair_b[i] = i < n_pairs ? p->pair_b[i] : 0;
+  }
+
+  // Time-major records: gather the electrode rows into the workspace, then engine 3 on those.
+  if ((p->engine == 0 || p->engine == 3) && p->time_major && chain_ok && !(p->crop & 3) && workspace &&
+      !(reinterpret_cast<uintptr_t>(workspace) & 15)) {
+    GatherRows rows;
+    MelArgs g3 = a;
+    rows.n = compact_rows(*p, rows.r, g3.pair_a, g3.pair_b);
+    const int n_rows = rows.n;
+    const size_t per_rec = (size_t)n_rows * p->crop * sizeof(float);
+    long long pass = (long long)(workspace_bytes / per_rec);
+    if (pass > kGatherChunk) pass = kGatherChunk;
+    if (pass >= 1 && (size_t)kGatherTile * (n_ch + 1) * sizeof(float) <= 48 * 1024) {
+      float* scratch = static_cast<float*>(workspace);
+      cudaError_t e;
+      eegspec_mel_params p3 = *p;
+      p3.time_major = 0;
+      g3.q = nullptr;
+      g3.refdb = nullptr;
+      g3.rec_stride = (long long)n_rows * p->crop;
+      g3.ch_stride = p->crop;
+      g3.t_stride = 1;
+      g3.length = p->crop;
+      g3.crop_off = 0;
+      int rc3 = EEGSPEC_OK;
+      for (long long r0 = 0; r0 < batch && rc3 == EEGSPEC_OK; r0 += pass) {
+        const long long nb = batch - r0 < pass ? batch - r0 : pass;
+        gather_rows_kernel<<<dim3((unsigned)((p->crop + kGatherTile - 1) / kGatherTile), (unsigned)nb), kGatherTile,
+                             (size_t)kGatherTile * (n_ch + 1) * sizeof(float), st>>>(
+            eeg + r0 * rec_stride, rec_stride, n_ch, a.crop_off, p->crop, rows, scratch);
+        count_launch();
+        if ((e = cudaGetLastError()) != cudaSuccess) return (int)e;
+        g3.eeg = scratch;
+        g3.out = out + r0 * (long long)p->n_mels * g.n_time * p->n_chains;
+        rc3 = melspec_chain_launch(g3, p3, nb, st);
+        if (rc3 == EEGSPEC_EUNSUPPORTED && r0 == 0) break;   // geometry not served: the scratch engines below
+      }
+      if (rc3 != EEGSPEC_EUNSUPPORTED) return rc3;
+    }
   }
 
   // Engine 3 (default when the geometry is the north-star one): one persistent launch, no scratch.

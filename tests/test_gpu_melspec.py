@@ -90,9 +90,22 @@ def test_single_record_time_major_and_crop():
     assert got.shape == (128, 256, 4)
     assert np.abs(got - want).max() <= ATOL
     tm = b200spec.spectrogram_from_eeg(torch.from_numpy(np.ascontiguousarray(x.T)).cuda())
-    assert np.abs(tm.cpu().numpy() - got).max() <= 1e-4      # time-major input runs on engine 2
+    assert np.abs(tm.cpu().numpy() - got).max() == 0.0       # parquet layout: electrode rows gathered, same engine
     mid = run(x[:, 4000:14000])
     assert np.abs(mid - got).max() == 0.0                    # crop offset is exact integer math
+
+
+def test_time_major_batch_equals_channel_major():
+    """The parquet layout (B, L, 20) goes through the row gather and the default engine: bit-identical
+    to the channel-major call, for a batch that spans more than one gather pass' worth of clusters."""
+    rng = np.random.default_rng(26)
+    x = torch.from_numpy(eeg_like(rng, (90, 20, 10400))).cuda()
+    x[3, 5, 700:900] = float("nan")
+    cm = b200spec.eeg_to_spectrogram(x)
+    tm = b200spec.eeg_to_spectrogram(x.transpose(1, 2).contiguous(), time_major=True)
+    assert torch.equal(cm, tm)
+    odd = x[:, :19].contiguous()                               # 19 channels: unaligned time-major rows (scalar gather)
+    assert torch.equal(b200spec.eeg_to_spectrogram(odd), b200spec.eeg_to_spectrogram(odd.transpose(1, 2).contiguous(), time_major=True))
 
 
 def test_chain_order_and_pair_wiring():
@@ -146,7 +159,7 @@ def test_host_front_door_and_determinism():
     nat.check(nat.lib.eegspec_melspec_host_bytes(130, 20, 10000, ctypes.byref(p), ctypes.byref(h2d), ctypes.byref(d2h)), "bytes")
     assert h2d.value == 130 * 16 * 10000 * 4 and d2h.value == out.numel() * 4
     tm = b200spec.eeg_to_spectrogram(x[:3].transpose(1, 2).contiguous(), time_major=True)   # parquet layout: one flat copy
-    assert (tm - out[:3]).abs().max().item() <= ATOL          # another engine reads time-major records
+    assert torch.equal(tm, out[:3])                              # gathered into electrode rows, same engine
 
 
 def test_errors():
