@@ -308,6 +308,20 @@ def main():
     }
 
     if "r" in legs:
+        # ------------------------------------------------------------ mode N on the parquet layout (L, 20)
+        x_tm = x_n.transpose(1, 2).contiguous()
+        p_tm = b200spec.mel_params(time_major=True)
+
+        def step_tm():
+            keep["tm"] = b200spec.eeg_to_spectrogram(x_tm, p_tm)
+
+        ms_tm, _ = timed(step_tm, args.steps, args.warmup)
+        result["time_major"] = {
+            "what": "the same records as (1024,10000,20) rows (the reference's parquet layout): row gather into the "
+                    "workspace + the default engine, bit-identical output",
+            "value": world * RECORDS * args.steps / (ms_tm * 1e-3), "unit": UNIT, "ms_per_step": ms_tm / args.steps}
+        del keep["tm"], x_tm
+
         # ------------------------------------------------------------ mode R, device resident
         def step_r50():
             keep["r"] = b200spec.compute_stft(x_n, Cfg)
@@ -413,11 +427,11 @@ def main():
             from oracle import cpu_bench
 
             arm = cpu_bench.CpuArm()
-            n_rec = max(arm.cores * 6, 48)
+            n_rec = max(arm.cores * 24, 192)    # ~20 core-seconds of the oracle port (20 records/s per core)
             c_n = arm.run("n", n_rec, seed=2)
-            c_r = arm.run("r10", max(arm.cores * 16, 128), seed=5)
-            c_r50 = arm.run("r50", max(arm.cores * 4, 32), seed=6)
-            c_xf = arm.run("xf", max(arm.cores * 8, 64), seed=7)
+            c_r = arm.run("r10", max(arm.cores * 64, 512), seed=5)
+            c_r50 = arm.run("r50", max(arm.cores * 16, 128), seed=6)
+            c_xf = arm.run("xf", max(arm.cores * 32, 256), seed=7)
             arm.close()
             if "eeg_transform" in result:
                 result["eeg_transform"]["cpu_baseline"] = {
