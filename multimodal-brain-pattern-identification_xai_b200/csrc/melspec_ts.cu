@@ -670,17 +670,21 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTThreads, 1) melspe
       const bool tr_now = q_tr >= 0 && (step & 1);
       const int rec_prev = cluster_id + q_tr * n_clusters;
       if (tr_now) transpose_load(rec_prev, step >> 1);   // L2 latency covered by the exchange wait and the fold
-      fold_tile(j);
-      if (warp == 0) TL(10);
-      if ((j + 1) % a.ppc == 0) {   // last pair of a chain: stash it, start afresh
-        chain_done(j);
+      // The chain that ended with tile j - 1 is stashed HERE, inside the exchange wait of tile j: its
+      // 64 KB of stores per CTA run into the SM's store throttle (~1 100 ns) and would sit on the
+      // critical path at the end of tile j - 1; the accumulators are not touched before fold j.
+      if (j > 0 && j % a.ppc == 0) {
+        chain_done(j - 1);
 #pragma unroll
         for (int i = 0; i < kTMels; ++i) acc[i] = 0.f;
         csum = 0.f;
       }
+      fold_tile(j);
+      if (warp == 0) TL(10);
       if (tr_now) transpose_store(rec_prev, step >> 1);
       if (warp == 0) TL(11);
     }
+    if (J > 0) chain_done(J - 1);
     // ---- the last record of this cluster: all groups at once
     {
       const int rec_last = cluster_id + (n_my_items - 1) * n_clusters;
