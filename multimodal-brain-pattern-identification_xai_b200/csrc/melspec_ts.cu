@@ -679,9 +679,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTThreads, 1) melspe
         for (int i = 0; i < kTMels; ++i) acc[i] = 0.f;
         csum = 0.f;
       }
+      if (tr_now) transpose_store(rec_prev, step >> 1);
       fold_tile(j);
       if (warp == 0) TL(10);
-      if (tr_now) transpose_store(rec_prev, step >> 1);
       if (warp == 0) TL(11);
     }
     if (J > 0) chain_done(J - 1);
