@@ -576,7 +576,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTThreads, 1) melspe
     };
     auto transpose_store = [&](int rec, int g) {
       float* r = row_seg(rec) + 4 * g * mstride + 4 * t_frame;
-      c_named_bar(3 + part, 128);
+      // no barrier: the four slots read and the four slots written are this thread's own (chain_done
+      // and this function address rows 4 g .. 4 g + 3 at the same 16 bytes, 4 t_frame)
       *reinterpret_cast<float4*>(r + 0 * mstride) = make_float4(tv[0].x, tv[1].x, tv[2].x, tv[3].x);
       *reinterpret_cast<float4*>(r + 1 * mstride) = make_float4(tv[0].y, tv[1].y, tv[2].y, tv[3].y);
       *reinterpret_cast<float4*>(r + 2 * mstride) = make_float4(tv[0].z, tv[1].z, tv[2].z, tv[3].z);
