@@ -61,7 +61,7 @@ static_assert(kTXCol + 4 * kTXN <= 512, "tensor memory budget");
 static_assert(MELGEN_COL0_P4_3 + 8 * MELGEN_CHUNKS_P4_3 <= kTBins, "the generated epilogue stays inside N");
 
 struct TsShared {
-  unsigned long long load_bar, stage_free, y_ready[2], y_free[2], ops_bar[2], afree_bar[2], mma_bar[2], tmem_free[2], xch_bar[2];
+  unsigned long long load_bar[2], stage_free, y_ready[2], y_free[2], ops_bar[2], afree_bar[2], mma_bar[2], tmem_free[2], xch_bar[2];
   uint32_t tmem_base;
   unsigned int xmax[4];             // this CTA's maximum of tile j (order-preserving uint of log2), [j & 3]
   __align__(16) float pv[2][kTEpiWarps];   // the peer's per-warp maxima of tile j (log2), [j & 1], written by st.async
@@ -143,8 +143,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTThreads, 1) melspe
   extern __shared__ __align__(128) unsigned char smem_raw[];
   unsigned char* tab = smem_raw;                                       // Ch | Cl | Sh | Sl
   float* ybuf = reinterpret_cast<float*>(tab + 4 * kCTabBytes);        // kTYFloats
-  float* stage = ybuf + 2 * kTYFloats;                                 // 2 x kCStageFloats (ybuf is double buffered)
-  unsigned char* xt = reinterpret_cast<unsigned char*>(stage + 2 * kCStageFloats);   // [j & 1]{Exh | Oxh}
+  float* stage = ybuf + 2 * kTYFloats;                                 // [j & 1]{row a | row b} x kCStageFloats (ybuf is double buffered too)
+  unsigned char* xt = reinterpret_cast<unsigned char*>(stage + 4 * kCStageFloats);   // [j & 1]{Exh | Oxh}
   unsigned char* xtab = xt + 4 * kTXTileBytes;   // extra frames: {cos hi | sin hi} with row r = bin r - r / 32 (128 rows each)
   __shared__ TsShared sh;
 
@@ -162,7 +162,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTThreads, 1) melspe
       a.tl[((blockIdx.x * kTlTilesT + (j - a.tl_j0)) * kTlSlotsT) + (slot)] = t_globaltimer();                                  \
   } while (0)
 
-  const uint32_t load_bar = c_smem_u32(&sh.load_bar), stage_free = c_smem_u32(&sh.stage_free);
+  const uint32_t load_bar0 = c_smem_u32(&sh.load_bar[0]), stage_free = c_smem_u32(&sh.stage_free);
   const uint32_t ops_bar0 = c_smem_u32(&sh.ops_bar[0]), afree0 = c_smem_u32(&sh.afree_bar[0]);
   const uint32_t mma_bar0 = c_smem_u32(&sh.mma_bar[0]), tmem_free0 = c_smem_u32(&sh.tmem_free[0]);
   const uint32_t xch_bar0 = c_smem_u32(&sh.xch_bar[0]);
@@ -171,7 +171,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTThreads, 1) melspe
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
   }
   if (tid == 32) {
-    c_mbar_init(load_bar, 1);
+    c_mbar_init(load_bar0, 1);
+    c_mbar_init(load_bar0 + 8, 1);
     c_mbar_init(stage_free, 2);
     for (int b = 0; b < 2; ++b) {
       c_mbar_init(ops_bar0 + 8 * b, kTBuildWarps);
@@ -312,17 +313,23 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTThreads, 1) melspe
           const float* base = a.eeg + rec * a.rec_stride + a.crop_off + seg_lo;
           const uint32_t bytes = (uint32_t)seg_n * 4u;
           asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+          const uint32_t load_bar = load_bar0 + 8 * (j & 1);
+          float* st = stage + (j & 1) * 2 * kCStageFloats;
           c_mbar_expect_tx(load_bar, 2 * bytes);
-          c_bulk_g2s(c_smem_u32(stage), base + a.pair_a[pr] * a.ch_stride, bytes, load_bar);
-          c_bulk_g2s(c_smem_u32(stage + kCStageFloats), base + a.pair_b[pr] * a.ch_stride, bytes, load_bar);
+          c_bulk_g2s(c_smem_u32(st), base + a.pair_a[pr] * a.ch_stride, bytes, load_bar);
+          c_bulk_g2s(c_smem_u32(st + kCStageFloats), base + a.pair_b[pr] * a.ch_stride, bytes, load_bar);
         };
         // Stagger the clusters by a quarter of a chain each: all CTAs do identical work and would
         // otherwise store their finished chains in the same instant (L2 write bursts).
         for (int k = 0; k < (cluster_id & 3); ++k) asm volatile("nanosleep.u32 %0;" ::"r"(a.stagger_ns));
+        // two staging buffers: the rows of pair j + 2 are requested as soon as the difference of pair j
+        // has left its buffer, a whole tile before they are needed (with one buffer the ~0.9 us of the
+        // copy sat on the difference warps' loop, which sets the kernel's period)
         issue_load(0);
-        for (int j = 0; j + 1 < J; ++j) {
+        if (J > 1) issue_load(1);
+        for (int j = 0; j + 2 < J; ++j) {
           c_mbar_wait(stage_free, j & 1);
-          issue_load(j + 1);
+          issue_load(j + 2);
         }
       }
     } else {
@@ -349,14 +356,14 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTThreads, 1) melspe
       };
       for (int j = 0; j < J; ++j) {
         float* yb = ybuf + (j & 1) * kTYFloats;
-        c_mbar_wait(load_bar, j & 1);
+        c_mbar_wait(load_bar0 + 8 * (j & 1), (j >> 1) & 1);
         if (dw == 0) TL(0);
         if (j >= 2) c_mbar_wait(y_free0 + 8 * (j & 1), ((j - 2) >> 1) & 1);   // the build group has read pair j - 2
         if (dw == 0) TL(1);
         float amax = 0.f;
         {
-          const float4* sa = reinterpret_cast<const float4*>(stage);
-          const float4* sb = reinterpret_cast<const float4*>(stage + kCStageFloats);
+          const float4* sa = reinterpret_cast<const float4*>(stage + (j & 1) * 2 * kCStageFloats);
+          const float4* sb = sa + kCStageFloats / 4;
           float4* yd = reinterpret_cast<float4*>(yb + kCMargin);
 #pragma unroll 4
           for (int i = dtid; i < (seg_n >> 2); i += kTDiff) {
@@ -706,7 +713,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTThreads, 1) melspe
 
 // ------------------------------------------------------------------------------------- host
 size_t melspec_ts_smem_bytes() {
-  return 4 * (size_t)kCTabBytes + sizeof(float) * (2 * (size_t)kTYFloats + 2 * (size_t)kCStageFloats) + 4 * (size_t)kTXTileBytes +
+  return 4 * (size_t)kCTabBytes + sizeof(float) * (2 * (size_t)kTYFloats + 4 * (size_t)kCStageFloats) + 4 * (size_t)kTXTileBytes +
          2 * 16384;   // remapped hi tables of the extra frames
 }
 
