@@ -168,6 +168,9 @@ typedef struct eegspec_xform_params {
   int32_t downsample;                  /* keep every downsample-th sample (1 = all), <= 8       */
   int32_t out_channel_major;           /* 0: out is (batch, L_out, n_out) like the reference;
                                         * 1: (batch, n_out, L_out), the layout compute_stft eats */
+  int32_t mu_law;                      /* 1: sign(y) log(1 + mu |y|) / log(1 + mu) after the filter
+                                        *    (dataset.py:98-99, 133-147)                          */
+  float mu;                            /* 1 (the reference calls _quantize_data(x, 1))            */
 } eegspec_xform_params;
 
 /* Defaults of CFG.dataset["eeg"] (cfg_utils.py:97-106): 19 selected channels, normalize,

@@ -44,7 +44,7 @@ class XformParams(C.Structure):
         ("n_out", C.c_int32), ("sel_a", C.c_int32 * MAX_XF_CH), ("sel_b", C.c_int32 * MAX_XF_CH),
         ("normalize", C.c_int32), ("clip_abs", C.c_float), ("scale", C.c_float), ("filter", C.c_int32),
         ("b", C.c_double * 5), ("a", C.c_double * 5), ("downsample", C.c_int32),
-        ("out_channel_major", C.c_int32),
+        ("out_channel_major", C.c_int32), ("mu_law", C.c_int32), ("mu", C.c_float),
     ]
 
 

@@ -36,13 +36,19 @@ struct XfArgs {
   const float* x;
   float* out;
   long long rec_stride, length, l_out;
-  int n_ch, n_out, ds, chunk, normalize, filter, out_channel_major;
-  float clip_abs, scale;
+  int n_ch, n_out, ds, chunk, normalize, filter, out_channel_major, mu_law;
+  float clip_abs, scale, mu, mu_scale;
   float b[EEGSPEC_XF_ORDER + 1], a[EEGSPEC_XF_ORDER + 1];
   float g[EEGSPEC_XF_ORDER][kXfP];                    // zero-input response of unit state i at sample m * ds
   double m[EEGSPEC_XF_ORDER][EEGSPEC_XF_ORDER];       // state after one chunk of zero input: s' = M s
   int sel_a[EEGSPEC_MAX_XF_CH], sel_b[EEGSPEC_MAX_XF_CH];
 };
+
+// mu-law companding of the filtered value (dataset.py:139-147): sign(y) log(1 + mu |y|) / log(1 + mu);
+// mu_scale = 1 / log2(1 + mu).  sign(0) = 0 and NaN stays NaN, like NumPy's.
+__device__ __forceinline__ float xf_mu_law(float y, float mu, float mu_scale) {
+  return copysignf(log2f(fmaf(mu, fabsf(y), 1.f)) * mu_scale, y);
+}
 
 // DS > 0: compile-time decimation with normalize / filter / difference fixed by NORM / FILT / DIFF
 // (straight-line recurrence: ~16 instructions per sample instead of ~42 with run-time switches,
@@ -149,6 +155,10 @@ __global__ void __launch_bounds__(kXfThreads) eeg_transform_kernel(const XfArgs 
       for (int m = 0; m < kXfP; ++m)
         yz[m] += a.g[0][m] * f0 + a.g[1][m] * f1 + a.g[2][m] * f2 + a.g[3][m] * f3;
     }
+    if (a.mu_law) {
+#pragma unroll
+      for (int m = 0; m < kXfP; ++m) yz[m] = xf_mu_law(yz[m], a.mu, a.mu_scale);
+    }
     // ---- store the decimated outputs of this chunk
     if (live) {
       const long long o0 = t0 / ds + (long long)k * kXfP;   // t0 and the chunk are multiples of ds
@@ -198,7 +208,8 @@ struct SpArgs {
   float* out;
   long long rec_stride, length, l_out;
   int n_out, units, span, stride, out_channel_major;   // span in samples (multiple of kSpChunk), stride in floats
-  float clip;
+  float clip, mu, mu_scale;
+  int mu_law;
   float b[EEGSPEC_XF_ORDER + 1], a[EEGSPEC_XF_ORDER + 1];   // b already multiplied by the scale
   float g[EEGSPEC_XF_ORDER][kSpP];
   float m[EEGSPEC_XF_ORDER][EEGSPEC_XF_ORDER], m2[EEGSPEC_XF_ORDER][EEGSPEC_XF_ORDER];   // over one chunk, over two
@@ -324,6 +335,10 @@ __global__ void __launch_bounds__(32 * kSpChunks) eeg_transform_span_kernel(cons
 #pragma unroll
       for (int m = 0; m < kSpP; ++m)
         yz[m] += a.g[0][m] * f[0] + a.g[1][m] * f[1] + a.g[2][m] * f[2] + a.g[3][m] * f[3];
+    }
+    if (a.mu_law) {
+#pragma unroll
+      for (int m = 0; m < kSpP; ++m) yz[m] = xf_mu_law(yz[m], a.mu, a.mu_scale);
     }
     if (live) {
       const long long o0 = t_chunk / kSpDs;
@@ -499,6 +514,10 @@ __global__ void __launch_bounds__(256) eeg_transform_lane_kernel(const SpArgs a)
 #pragma unroll
     for (int m = 0; m < kSpP; ++m)
       yz[m] += a.g[0][m] * f[0] + a.g[1][m] * f[1] + a.g[2][m] * f[2] + a.g[3][m] * f[3];
+    if (a.mu_law) {
+#pragma unroll
+      for (int m = 0; m < kSpP; ++m) yz[m] = xf_mu_law(yz[m], a.mu, a.mu_scale);
+    }
 
     if (live) {
       const int o0 = t_chunk / kSpDs;
@@ -567,6 +586,8 @@ void xform_params_default(eegspec_xform_params* p) {
   }
   p->downsample = 5;
   p->out_channel_major = 0;
+  p->mu_law = 0;
+  p->mu = 1.f;
 }
 
 long long xform_out_length(long long length, const eegspec_xform_params* p) {
@@ -587,6 +608,9 @@ static int span_launch(const float* x, long long batch, long long length, int n_
   a.n_out = p->n_out;
   a.out_channel_major = p->out_channel_major;
   a.clip = p->clip_abs;
+  a.mu_law = p->mu_law;
+  a.mu = p->mu;
+  a.mu_scale = 1.f / log2f(1.f + p->mu);
   for (int i = 0; i <= EEGSPEC_XF_ORDER; ++i) { a.b[i] = (float)(p->b[i] * (double)p->scale); a.a[i] = (float)p->a[i]; }
   for (int c = 0; c < EEGSPEC_MAX_XF_CH; ++c) { a.sel_a[c] = p->sel_a[c]; a.sel_b[c] = p->sel_b[c] < 0 ? 0 : p->sel_b[c]; }
   double decay = 0.0;   // largest entry of the state transition over the warm-up (three chunks)
@@ -662,6 +686,7 @@ int eeg_transform_launch(const float* x, long long batch, long long length, int 
   for (int c = 0; c < p->n_out; ++c)
     if (p->sel_a[c] < 0 || p->sel_a[c] >= n_ch || p->sel_b[c] >= n_ch) return EEGSPEC_EINVAL;
   if (p->filter && fabs(p->a[0] - 1.0) > 1e-12) return EEGSPEC_EINVAL;
+  if (p->mu_law && !(p->mu > 0.f)) return EEGSPEC_EINVAL;
 
   XfArgs a;
   a.x = x;
@@ -678,6 +703,9 @@ int eeg_transform_launch(const float* x, long long batch, long long length, int 
   a.out_channel_major = p->out_channel_major;
   a.clip_abs = p->clip_abs;
   a.scale = p->scale;
+  a.mu_law = p->mu_law;
+  a.mu = p->mu;
+  a.mu_scale = 1.f / log2f(1.f + p->mu);
   for (int i = 0; i <= EEGSPEC_XF_ORDER; ++i) { a.b[i] = (float)p->b[i]; a.a[i] = (float)p->a[i]; }
   for (int c = 0; c < EEGSPEC_MAX_XF_CH; ++c) { a.sel_a[c] = p->sel_a[c]; a.sel_b[c] = p->sel_b[c]; }
   for (int i = 0; i < EEGSPEC_XF_ORDER; ++i) {   // unit state i, zero input, one chunk

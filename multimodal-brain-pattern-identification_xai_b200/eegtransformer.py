@@ -7,7 +7,7 @@
 * it also accepts a batch ``(B, L, C)`` (the reference loops over records in Python);
 * the result is float32 on the input's device (the reference returns float64 from
   ``scipy.signal.lfilter``); NumPy in -> NumPy out, tensor in -> tensor out;
-* ``apply_mu_law_encoding=True`` raises ``NotImplementedError`` (no CUDA path, no fallback);
+* ``apply_mu_law_encoding=True`` compands with mu = 1 like the reference (``_quantize_data(x_, 1)``);
 * ``channel_major=True`` returns ``(B, n_out, L_out)``, the layout ``compute_stft`` consumes.
 
 The arithmetic runs in ``csrc/eegtransform.cu`` behind ``eegspec_eeg_transform_f32``.
@@ -31,7 +31,7 @@ EEG_PTS = 10000        # CFG.EEG_PTS, cfg_utils.py:75
 
 def xform_params(n_feats: int = 19, apply_chris_magic_ch8: bool = False, normalize: bool = True,
                  apply_butter_lowpass_filter: bool = True, downsample: Optional[int] = None,
-                 channel_major: bool = False) -> nat.XformParams:
+                 channel_major: bool = False, apply_mu_law_encoding: bool = False) -> nat.XformParams:
     p = nat.XformParams()
     nat.lib.eegspec_xform_params_default(C.byref(p))     # Butterworth (4, 20 Hz @ 200 Hz) in double precision
     if apply_chris_magic_ch8:
@@ -50,6 +50,8 @@ def xform_params(n_feats: int = 19, apply_chris_magic_ch8: bool = False, normali
     if p.downsample < 1:
         raise ValueError("downsample must be a positive integer or None")
     p.out_channel_major = int(bool(channel_major))
+    p.mu_law = int(bool(apply_mu_law_encoding))       # dataset.py:98-99: _quantize_data(x_, 1) -> mu = 1
+    p.mu = 1.0
     return p
 
 
@@ -59,8 +61,6 @@ class EEGTransformer:
     def __init__(self, n_feats: int, apply_chris_magic_ch8: bool = False, normalize: bool = True,
                  apply_butter_lowpass_filter: bool = True, apply_mu_law_encoding: bool = False,
                  downsample: Optional[int] = None, channel_major: bool = False) -> None:
-        if apply_mu_law_encoding:
-            raise NotImplementedError("mu-law quantisation (dataset.py:133-147) has no CUDA path")
         self.n_feats = n_feats
         self.apply_chris_magic_ch8 = apply_chris_magic_ch8
         self.normalize = normalize
@@ -68,7 +68,7 @@ class EEGTransformer:
         self.apply_mu_law_encoding = apply_mu_law_encoding
         self.downsample = downsample
         self.params = xform_params(n_feats, apply_chris_magic_ch8, normalize, apply_butter_lowpass_filter,
-                                   downsample, channel_major)
+                                   downsample, channel_major, apply_mu_law_encoding)
 
     def transform(self, x):
         """x: (L, C) or (B, L, C) raw EEG, time-major like the reference's arrays."""

@@ -10,7 +10,8 @@ Follows ``_EEGTransformer.transform`` (/root/reference/root/src/data/dataset.py:
 2. ``np.clip(x_, -1024, 1024)`` then ``np.nan_to_num(x_, nan=0) / 32.0`` (:92-94);
 3. ``butter(4, 20 / 100, btype="low")`` + ``lfilter(b, a, data, axis=0)`` (:125-131): a causal IIR
    along time, SciPy's direct form II transposed, float64;
-4. ``x_[::downsample, :]`` (:101-102).
+4. optional mu-law companding ``sign(x) log(1 + mu |x|) / log(mu + 1)`` with mu = 1 (:98-99, :133-147);
+5. ``x_[::downsample, :]`` (:101-102).
 
 PINNED: ``tests/test_oracle_eegtransform.py`` checks this restatement against the reference's own
 class executed through ``oracle/ref_extract.py`` (when /root/reference is present) and against
@@ -49,7 +50,8 @@ def lfilter_df2t(b, a, x):
 
 
 def eeg_transform_oracle(x, n_feats=19, apply_chris_magic_ch8=False, normalize=True,
-                         apply_butter_lowpass_filter=True, downsample=None, use_scipy=True):
+                         apply_butter_lowpass_filter=True, downsample=None, use_scipy=True,
+                         apply_mu_law_encoding=False):
     """x: (L, C) raw EEG of one record -> (ceil(L / downsample), n_out) float64."""
     x_ = np.array(x, copy=True)
     if apply_chris_magic_ch8:
@@ -70,6 +72,9 @@ def eeg_transform_oracle(x, n_feats=19, apply_chris_magic_ch8=False, normalize=T
             x_ = lfilter(b, a, x_, axis=0)
         else:
             x_ = lfilter_df2t(b, a, x_)
+    if apply_mu_law_encoding:
+        mu = 1                                         # dataset.py:99: self._quantize_data(x_, 1)
+        x_ = np.sign(x_) * np.log(1 + mu * np.abs(x_)) / np.log(mu + 1)
     if downsample is not None:
         x_ = x_[::downsample, :]
     return x_

@@ -129,6 +129,9 @@ XFORM_CASES = {
     "no_downsample": (2000, 20, dict(n_feats=19), "eeg"),
     "no_filter_ds4": (3001, 20, dict(n_feats=19, apply_butter_lowpass_filter=False, downsample=4), "eeg"),
     "raw_scale": (2403, 20, dict(n_feats=19, normalize=False, downsample=3), "eeg"),
+    # appended later: the draws above are unchanged
+    "mu_law": (10000, 20, dict(n_feats=19, apply_mu_law_encoding=True, downsample=5), "eeg"),
+    "mu_law_nofilter_nan": (3000, 20, dict(n_feats=19, apply_butter_lowpass_filter=False, apply_mu_law_encoding=True, downsample=2), "nan"),
 }
 
 

@@ -63,8 +63,6 @@ def test_feeds_compute_stft():
 
 
 def test_errors():
-    with pytest.raises(NotImplementedError):
-        b200spec.EEGTransformer(n_feats=19, apply_mu_law_encoding=True)
     with pytest.raises(ValueError):
         b200spec.EEGTransformer(n_feats=19).transform(torch.zeros(100, 10, device="cuda"))      # too few channels
     with pytest.raises(ValueError):

@@ -16,6 +16,8 @@ CASES = {
     "no_downsample": dict(n_feats=19),
     "no_filter_ds4": dict(n_feats=19, apply_butter_lowpass_filter=False, downsample=4),
     "raw_scale": dict(n_feats=19, normalize=False, downsample=3),
+    "mu_law": dict(n_feats=19, apply_mu_law_encoding=True, downsample=5),
+    "mu_law_nofilter_nan": dict(n_feats=19, apply_butter_lowpass_filter=False, apply_mu_law_encoding=True, downsample=2),
 }
 
 
@@ -23,7 +25,8 @@ CASES = {
 def test_oracle_matches_reference_golden(eegtransform_golden, name):
     x, want = eegtransform_golden[f"{name}/x"], eegtransform_golden[f"{name}/y"]
     got = eo.eeg_transform_oracle(x, **CASES[name])
-    assert got.shape == want.shape and got.dtype == (np.float64 if CASES[name].get("apply_butter_lowpass_filter", True) else np.float32)
+    f64 = CASES[name].get("apply_butter_lowpass_filter", True) or CASES[name].get("apply_mu_law_encoding", False)
+    assert got.shape == want.shape and got.dtype == (np.float64 if f64 else np.float32)
     np.testing.assert_allclose(got, want, rtol=0, atol=1e-12, equal_nan=True)   # same SciPy calls: bit-level agreement
 
 
