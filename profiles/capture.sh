@@ -27,4 +27,5 @@ cap melspec_ts melspec_ts_kernel 3
 cap stft_hms50s stft_image_kernel 3
 cap stft_diffeeg stft_image_kernel 8
 cap eeg_transform eeg_transform_lane_kernel 3
+cap gather gather_rows_kernel 3
 ls -la $OUT
