@@ -101,6 +101,17 @@ def test_host_door_byte_count():
     assert nat.lib.eegspec_melspec_host_bytes(7, 0, 10000, C.byref(p), C.byref(h2d), None) == nat.EINVAL
 
 
+def test_workspace_covers_the_time_major_gather():
+    """Time-major (parquet-layout) records are gathered into electrode rows inside the caller's
+    workspace: 16 rows x crop floats per record for up to 1 024 records per pass."""
+    cm, tm = b200spec.mel_params(), b200spec.mel_params(time_major=True)
+    for batch in (1, 64, 1024, 5000):
+        need_cm = nat.lib.eegspec_melspec_workspace(batch, C.byref(cm))
+        need_tm = nat.lib.eegspec_melspec_workspace(batch, C.byref(tm))
+        assert need_tm >= need_cm > 0
+        assert need_tm >= min(batch, 1024) * 16 * 10000 * 4
+
+
 def test_montage_constants_match_oracle():
     from b200spec import montage
 
