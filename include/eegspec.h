@@ -127,6 +127,18 @@ int eegspec_melspec_f32(const float *eeg, int64_t batch, int32_t n_ch, int64_t l
                         int64_t rec_stride, const eegspec_mel_params *p, float *out,
                         void *workspace, size_t workspace_bytes, void *stream);
 
+/* Sliding windows over ONE long record (BASELINE.json configs[3]: a 1-hour EEG cut into overlapping
+ * 50-s windows).  Window w is samples [w*stride, w*stride + p->crop) of the series -- the window
+ * /root/reference/root/src/utils/cfg_utils.py:369-371 cuts around one label offset, taken at every
+ * stride.  eeg: device fp32, (n_ch, total_length) channel-major, or (total_length, n_ch) when
+ * p->time_major.  The windows are read in place (nothing is materialised: 57.6 MB in for a 1-hour
+ * record instead of 1.4 GB of copies).  out: device (n_windows, n_mels, n_time, n_chains) fp32.
+ * Needs (n_windows - 1) * stride + p->crop <= total_length; workspace as eegspec_melspec_f32 with
+ * batch = n_windows. */
+int eegspec_melspec_sliding_f32(const float *eeg, int32_t n_ch, int64_t total_length, int64_t stride,
+                                int64_t n_windows, const eegspec_mel_params *p, float *out,
+                                void *workspace, size_t workspace_bytes, void *stream);
+
 /* ------------------------------------------------------------------------------------------
  * Host-buffer front doors (what the reference's caller has: CPU tensors from a DataLoader).
  * x / out are HOST pointers (pinned for full PCIe speed; pageable works, slower).  The call

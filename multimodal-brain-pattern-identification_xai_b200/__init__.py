@@ -6,6 +6,7 @@ KC-decoder/Multimodal-Brain-Pattern-Identification_XAI:
 * ``compute_stft(signal, config)``      -- /root/reference/root/src/utils/DiffEEG_utils.py:27-76
 * ``compute_stft_single(signal, config)`` -- DiffEEG_utils.py:504-509
 * ``eeg_to_spectrogram(eeg)``           -- the 4-chain x 128-mel image BASELINE.json names
+* ``eeg_to_spectrogram_sliding(eeg)``   -- the same image for every overlapping window of one long record
 * ``EEGTransformer(...).transform(x)``   -- ``_EEGTransformer``, /root/reference/root/src/data/dataset.py:48-104
 * ``install()``                         -- rebinds ``compute_stft`` inside the reference's modules
 
@@ -23,6 +24,8 @@ _API = {
     "interp_bracket": "transform",
     "eeg_to_spectrogram": "transform",
     "spectrogram_from_eeg": "transform",
+    "eeg_to_spectrogram_sliding": "transform",
+    "sliding_window_count": "transform",
     "mel_params": "transform",
     "melspec_geometry": "transform",
     "install": "transform",

@@ -67,6 +67,9 @@ SIGNATURES = {
     "eegspec_melspec_f32": (C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_int64, C.c_int64,
                                       C.POINTER(MelParams), C.c_void_p, C.c_void_p, C.c_size_t,
                                       C.c_void_p]),
+    "eegspec_melspec_sliding_f32": (C.c_int, [C.c_void_p, C.c_int32, C.c_int64, C.c_int64, C.c_int64,
+                                              C.POINTER(MelParams), C.c_void_p, C.c_void_p, C.c_size_t,
+                                              C.c_void_p]),
     "eegspec_stft_image_host_f32": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, C.c_int, C.c_int,
                                               C.c_int64, C.c_float, C.c_void_p, C.c_int]),
     "eegspec_melspec_host_f32": (C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_int64,

@@ -176,6 +176,13 @@ int eegspec_melspec_f32(const float* eeg, int64_t batch, int32_t n_ch, int64_t l
                         static_cast<cudaStream_t>(stream));
 }
 
+int eegspec_melspec_sliding_f32(const float* eeg, int32_t n_ch, int64_t total_length, int64_t stride,
+                                int64_t n_windows, const eegspec_mel_params* p, float* out, void* workspace,
+                                size_t workspace_bytes, void* stream) {
+  return melspec_sliding_launch(eeg, n_ch, total_length, stride, n_windows, p, out, workspace, workspace_bytes,
+                                static_cast<cudaStream_t>(stream));
+}
+
 int eegspec_stft_image_host_f32(const float* x, int64_t rows, int64_t length, int nperseg,
                                 int noverlap, int64_t out_cols, float eps, float* out,
                                 int device) {

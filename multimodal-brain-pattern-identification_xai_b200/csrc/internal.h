@@ -32,6 +32,12 @@ size_t melspec_workspace(long long batch, const eegspec_mel_params* p);
 int melspec_launch(const float* eeg, long long batch, int n_ch, long long length,
                    long long rec_stride, const eegspec_mel_params* p, float* out, void* workspace,
                    size_t workspace_bytes, cudaStream_t st);
+int melspec_launch_strided(const float* eeg, long long batch, int n_ch, long long length, long long rec_stride,
+                           long long ch_stride, const eegspec_mel_params* p, float* out, void* workspace,
+                           size_t workspace_bytes, cudaStream_t st);
+int melspec_sliding_launch(const float* eeg, int n_ch, long long total_length, long long stride, long long n_windows,
+                           const eegspec_mel_params* p, float* out, void* workspace, size_t workspace_bytes,
+                           cudaStream_t st);
 
 // eegtransform.cu
 void xform_params_default(eegspec_xform_params* p);

@@ -556,11 +556,34 @@ static size_t pair_kernel_smem(const eegspec_mel_params& p) {
 int melspec_launch(const float* eeg, long long batch, int n_ch, long long length,
                    long long rec_stride, const eegspec_mel_params* p, float* out, void* workspace,
                    size_t workspace_bytes, cudaStream_t st) {
+  if (rec_stride < (long long)n_ch * length) return EEGSPEC_EINVAL;
+  return melspec_launch_strided(eeg, batch, n_ch, length, rec_stride, p && p->time_major ? 1 : length, p, out,
+                                workspace, workspace_bytes, st);
+}
+
+// Sliding windows over one long record (BASELINE configs[3]): window w is a "record" that starts
+// w * stride samples into the series, so consecutive records overlap and nothing is materialised --
+// channel-major the electrode rows stay `total_length` apart, time-major a sample row is n_ch wide.
+int melspec_sliding_launch(const float* eeg, int n_ch, long long total_length, long long stride, long long n_windows,
+                           const eegspec_mel_params* p, float* out, void* workspace, size_t workspace_bytes,
+                           cudaStream_t st) {
+  if (!p) return EEGSPEC_EINVAL;
+  if (stride <= 0 || n_windows <= 0 || total_length <= 0) return EEGSPEC_EINVAL;
+  if (total_length < p->crop || (n_windows - 1) * stride + p->crop > total_length) return EEGSPEC_ESHORT;
+  return melspec_launch_strided(eeg, n_windows, n_ch, p->crop, p->time_major ? stride * n_ch : stride,
+                                p->time_major ? 1 : total_length, p, out, workspace, workspace_bytes, st);
+}
+
+// `length` samples of every record are addressed as eeg[rec * rec_stride + ch * ch_stride + t * t_stride]
+// with t_stride = n_ch for time-major records and 1 otherwise; records may overlap.
+int melspec_launch_strided(const float* eeg, long long batch, int n_ch, long long length, long long rec_stride,
+                           long long ch_stride, const eegspec_mel_params* p, float* out, void* workspace,
+                           size_t workspace_bytes, cudaStream_t st) {
   int rc = validate(p);
   if (rc != EEGSPEC_OK) return rc;
   if (!eeg || !out || batch <= 0 || n_ch <= 0) return EEGSPEC_EINVAL;
   if (length < p->crop) return EEGSPEC_ESHORT;
-  if (rec_stride < (long long)n_ch * length) return EEGSPEC_EINVAL;
+  if (rec_stride <= 0 || ch_stride <= 0) return EEGSPEC_EINVAL;
   if (reinterpret_cast<uintptr_t>(out) & 15) return EEGSPEC_EALIGN;
   const int n_pairs = p->n_chains * p->pairs_per_chain;
   for (int i = 0; i < n_pairs; ++i)
@@ -572,7 +595,7 @@ int melspec_launch(const float* eeg, long long batch, int n_ch, long long length
   bool chain_ok = false;
   if ((rc = device_tables(*p, &a.t, &g, &chain_ok)) != EEGSPEC_OK) return rc;
   a.rec_stride = rec_stride;
-  a.ch_stride = p->time_major ? 1 : length;
+  a.ch_stride = ch_stride;
   a.t_stride = p->time_major ? n_ch : 1;
   a.length = length;
   a.crop = p->crop;

@@ -208,6 +208,60 @@ def eeg_to_spectrogram(eeg: torch.Tensor, params: Optional[nat.MelParams] = None
     return out[0] if single else out
 
 
+def sliding_window_count(total_length: int, window: int = 10000, stride: int = 400) -> int:
+    """Number of whole ``window``-sample windows at every ``stride`` samples (0 if the record is shorter)."""
+    return 0 if total_length < window else (total_length - window) // stride + 1
+
+
+def eeg_to_spectrogram_sliding(eeg: torch.Tensor, window: int = 10000, stride: int = 400,
+                               params: Optional[nat.MelParams] = None, **kwargs) -> torch.Tensor:
+    """One long record -> the log-mel image of every overlapping window (BASELINE configs[3]).
+
+    ``eeg``: (20, L) fp32 channel-major (or (L, 20) with ``time_major=True``), e.g. a 1-hour
+    recording, L = 720 000.  Window ``w`` is samples ``[w*stride, w*stride + window)`` -- the 50-s
+    window ``cfg_utils.py:369-371`` cuts, taken every ``stride`` samples (400 = 2 s, the HMS
+    label-offset granularity).  Returns (n_windows, 128, 256, 4); row ``w`` is bit-identical to
+    ``eeg_to_spectrogram`` of the materialised slice.  The windows are read in place by the kernel:
+    the record is moved (and, for a host tensor, copied to the device) once, not once per window.
+    """
+    _require_cuda()
+    params = params if params is not None else mel_params(**kwargs)
+    if window != params.crop:
+        params = _copy_params(params)
+        params.crop = int(window)
+    x = _as_f32(eeg)
+    if x.dim() != 2:
+        raise ValueError("eeg must be one (n_ch, L) record (or (L, n_ch) with time_major=True)")
+    if stride <= 0:
+        raise ValueError("stride must be positive")
+    n_ch, total = (x.shape[1], x.shape[0]) if params.time_major else (x.shape[0], x.shape[1])
+    n_win = sliding_window_count(total, window, stride)
+    _, n_time = melspec_geometry(params)
+    shape = (n_win, params.n_mels, n_time, params.n_chains)
+    if n_win == 0:
+        return torch.empty(shape, dtype=torch.float32, device=eeg.device)
+    on_host = not x.is_cuda
+    xd = x.contiguous().cuda(non_blocking=True) if on_host else x.contiguous()
+    with torch.cuda.device(xd.device):
+        out = torch.empty(shape, dtype=torch.float32, device=xd.device)
+        ws_bytes = nat.lib.eegspec_melspec_workspace(n_win, C.byref(params))
+        ws = torch.empty(ws_bytes, dtype=torch.uint8, device=xd.device)
+        nat.check(nat.lib.eegspec_melspec_sliding_f32(_ptr(xd), n_ch, total, stride, n_win, C.byref(params),
+                                                      _ptr(out), _ptr(ws), ws_bytes, _stream_ptr(xd.device)),
+                  "eeg_to_spectrogram_sliding")
+    if on_host:
+        host = torch.empty(shape, dtype=torch.float32, pin_memory=True)
+        host.copy_(out)
+        return host
+    return out
+
+
+def _copy_params(params: nat.MelParams) -> nat.MelParams:
+    q = nat.MelParams()
+    C.memmove(C.byref(q), C.byref(params), C.sizeof(nat.MelParams))
+    return q
+
+
 def spectrogram_from_eeg(eeg: torch.Tensor, **kwargs) -> torch.Tensor:
     """One parquet-ordered record (L, 20) -> (128, 256, 4); the name the public HMS recipe uses."""
     if eeg.dim() != 2:

@@ -106,3 +106,70 @@ def load_reference_eeg_transformer():
     env = {"np": np, "butter": butter, "lfilter": lfilter, "Optional": Optional, "CFG": reference_cfg_channels()}
     exec(compile(module, _DATASET, "exec"), env)  # noqa: S102 - the reference's own code
     return env["_EEGTransformer"]
+
+
+# --------------------------------------------------------------------------- generic lift
+_DATA_UTILS = os.path.join(REFERENCE_ROOT, "root", "src", "utils", "data_utils.py")
+_CONFIG_YML = os.path.join(REFERENCE_ROOT, "root", "config", "config.yml")
+
+
+def lift_functions(path: str, names, env: dict) -> dict:
+    """Execute the top-level ``def``s called ``names`` of the reference file ``path`` inside
+    ``env`` (the free names they use) and return ``env``.  Nothing else of the module runs."""
+    with open(path, "r", encoding="utf-8") as fh:
+        tree = ast.parse(fh.read(), filename=path)
+    body = [n for n in tree.body if isinstance(n, (ast.FunctionDef, ast.ClassDef)) and n.name in set(names)]
+    missing = set(names) - {n.name for n in body}
+    if missing:
+        raise KeyError(f"{path}: no top-level definition of {sorted(missing)}")
+    module = ast.Module(body=body, type_ignores=[])
+    ast.fix_missing_locations(module)
+    exec(compile(module, path, "exec"), env)  # noqa: S102 - the reference's own code
+    return env
+
+
+def reference_yaml_config() -> dict:
+    """``root/config/config.yml`` as ``load_config`` reads it (config_loader.py:16-28; the
+    ``${root_dir}`` substitution only touches path strings, which nothing here uses)."""
+    import yaml
+
+    with open(_CONFIG_YML, "r", encoding="utf-8") as fh:
+        return yaml.safe_load(fh)
+
+
+def load_reference_get_eeg_window(use_magic_8: bool = False):
+    """The reference ``_get_eeg_window(file)`` (/root/reference/root/src/utils/cfg_utils.py:354-389):
+    parquet -> middle 10 000-sample crop -> per-channel NaN fill.  ``CFG`` is a stub holding the
+    reference's own literals (channel lists, ``cast_eegs = True``, the magic-8 switch)."""
+    from pathlib import Path
+
+    import numpy as np
+    import pandas as pd
+
+    lit = reference_cfg_channels()
+    cfg = SimpleNamespace(feats=lit.feats, channel_feats=lit.channel_feats, EEG_PTS=lit.EEG_PTS, cast_eegs=True,
+                          dataset={"eeg": {"apply_chris_magic_ch8": bool(use_magic_8)}})
+    env = {"np": np, "pd": pd, "Path": Path, "CFG": cfg, "EEG_PTS": cfg.EEG_PTS}
+    return lift_functions(_CFG_UTILS, ["_get_eeg_window"], env)["_get_eeg_window"], cfg
+
+
+def load_reference_data_utils(names, feature_names=None):
+    """Functions of ``root/src/utils/data_utils.py`` (e.g. ``calculate_differential_signals`` :183-215,
+    ``butter_bandpass_filter`` :224-226, ``normalize`` :230-233, ``denoise_filter`` :236-240) with the
+    module-level names they read: ``CFG`` = the YAML dict (:41) and ``feature_to_index`` (:42; built from
+    ``feature_names``, default the YAML's own ``eeg_features``)."""
+    import numpy as np
+    from scipy.ndimage import gaussian_filter
+    from scipy.signal import butter, filtfilt, iirnotch, lfilter
+
+    cfg = reference_yaml_config()
+    feats = list(feature_names) if feature_names is not None else cfg["eeg_features"]
+    env = {"np": np, "butter": butter, "lfilter": lfilter, "filtfilt": filtfilt, "iirnotch": iirnotch,
+           "gaussian_filter": gaussian_filter, "CFG": cfg,
+           "feature_to_index": {x: y for x, y in zip(feats, range(len(feats)))}}
+    try:
+        from skimage.transform import resize
+        env["resize"] = resize
+    except Exception:   # skimage is not in this image; only resample_spectrogram needs it
+        pass
+    return lift_functions(_DATA_UTILS, names, env)
