@@ -39,6 +39,16 @@ def melspec_golden():
     return np.load(os.path.join(GOLDEN_DIR, "melspec_golden.npz"))
 
 
+@pytest.fixture(scope="session")
+def fronthalf_golden():
+    return np.load(os.path.join(GOLDEN_DIR, "fronthalf_golden.npz"))
+
+
+@pytest.fixture(scope="session")
+def melspec_xcheck():
+    return np.load(os.path.join(GOLDEN_DIR, "melspec_xcheck.npz"))
+
+
 def eeg_like(rng, shape, walk=0.3, noise=1.0):
     """Synthetic EEG of SURVEY.md section 8d: random walk + 10 Hz sine + white noise, clipped."""
     x = np.cumsum(rng.standard_normal(shape), axis=-1) * walk

@@ -160,9 +160,107 @@ def make_eegtransform():
     print("wrote", path, os.path.getsize(path), "bytes")
 
 
+def make_fronthalf():
+    """``fronthalf_golden.npz``: inputs and outputs of the REFERENCE's own ``_get_eeg_window``
+    (/root/reference/root/src/utils/cfg_utils.py:354-389: parquet -> middle crop -> per-channel NaN
+    fill) and ``calculate_differential_signals`` (/root/reference/root/src/utils/data_utils.py:183-215),
+    lifted by ``oracle/ref_extract.py`` and run on temporary parquet files.  These pin
+    ``crop_offset`` / ``fill_missing`` / ``montage_differences`` of the mode-N oracle."""
+    import tempfile
+
+    import pandas as pd
+    import pyarrow
+
+    rng = np.random.default_rng(20261107)
+    out = {}
+    for name, n_pts in (("odd", 10001), ("longodd", 13579)):
+        x = np.round(eeg_like(rng, (n_pts, 20)))                # integer microvolts: the fixture compresses
+        x[rng.random((n_pts,)) < 0.01, 2] = np.nan              # scattered holes
+        x[n_pts // 2 - 40:n_pts // 2 + 40, 5] = np.nan          # a run inside the crop window
+        x[:300, 9] = np.nan                                     # a run that the crop may cut off
+        x[:, 14] = np.nan                                       # a dead electrode
+        out[f"window/{name}/x"] = x
+        with tempfile.TemporaryDirectory() as tmp:
+            path = os.path.join(tmp, "eeg.parquet")
+            pd.DataFrame(x, columns=mo.EEG_COLUMNS).to_parquet(path)
+            for magic in (False, True):
+                fn, cfg = rx.load_reference_get_eeg_window(use_magic_8=magic)
+                with np.errstate(all="ignore"):
+                    import warnings
+                    with warnings.catch_warnings():
+                        warnings.simplefilter("ignore")
+                        win = fn(path)
+                out[f"window/{name}/{'magic8' if magic else 'full19'}"] = win
+                out[f"channels/{'magic8' if magic else 'full19'}"] = np.array(cfg.feats if magic else cfg.channel_feats)
+    x = np.round(eeg_like(rng, (20, 600))).astype(np.float64)
+    x[3, 100:110] = np.nan
+    out["diff/x"] = x
+    env = rx.load_reference_data_utils(["calculate_differential_signals"], feature_names=mo.EEG_COLUMNS)
+    out["diff/eeg_columns"] = env["calculate_differential_signals"](x)              # (20 + 18, 600)
+    env = rx.load_reference_data_utils(["calculate_differential_signals"])            # the YAML's own 19 eeg_features
+    out["diff/yaml_features"] = env["calculate_differential_signals"](x[:19])         # (19 + 18, 600)
+    out["diff/yaml_feature_names"] = np.array(rx.reference_yaml_config()["eeg_features"])
+    out["versions"] = np.array([f"numpy {np.__version__}", f"pandas {pd.__version__}", f"pyarrow {pyarrow.__version__}"])
+    path = os.path.join(HERE, "fronthalf_golden.npz")
+    np.savez_compressed(path, **out)
+    print("wrote", path, os.path.getsize(path), "bytes")
+
+
+def xcheck_image(x):
+    """(20, L) EEG -> (128, 256, 4) with LIBRARY code only for the back half: torchaudio's
+    MelSpectrogram (torch.stft + melscale_fbanks) and amplitude_to_DB.  Nothing of oracle/ is used
+    except the montage table; the front half is three NumPy lines (difference, nanmean fill)."""
+    import torch
+    import torchaudio
+
+    mel = torchaudio.transforms.MelSpectrogram(
+        sample_rate=200, n_fft=1024, win_length=128, hop_length=39, f_min=0.0, f_max=20.0, n_mels=128,
+        window_fn=torch.hann_window, power=2.0, center=True, pad_mode="constant", norm="slaney",
+        mel_scale="slaney").double()
+    off = (x.shape[1] - 10000) // 2
+    w = x[:, off:off + 10000]
+    img = np.zeros((128, 256, 4), np.float32)
+    pairs = mo.pair_indices(16)
+    for k in range(4):
+        for kk in range(4):
+            a, b = pairs[4 * k + kk]
+            y = w[a] - w[b]
+            if np.isnan(y).all():
+                y = np.zeros_like(y)
+            elif np.isnan(y).any():
+                y = np.where(np.isnan(y), np.nanmean(y), y)
+            m = mel(torch.from_numpy(y.astype(np.float32)).double()).float()         # (128, 257)
+            ref = float(m.max())
+            db = torchaudio.functional.amplitude_to_DB(m[None], 10.0, 1e-10, float(np.log10(max(1e-10, ref))), 80.0)[0]
+            img[:, :, k] += ((db[:, :256] + 40.0) / 40.0).numpy()
+        img[:, :, k] /= 4.0
+    return img
+
+
+def make_melspec_xcheck():
+    """``melspec_xcheck.npz``: a SECOND, independent mode-N image from library code (torchaudio), on the
+    inputs of ``melspec_golden.npz``.  It narrows -- it does not close -- "parity unpinned": torchaudio
+    is not librosa, but its Slaney bank, centred constant-pad STFT and dB conversion are independent of
+    everything written in this repository."""
+    import torch
+    import torchaudio
+
+    gold = np.load(os.path.join(HERE, "melspec_golden.npz"))
+    out = {}
+    for case in ("clean", "nan", "range"):
+        out[f"{case}/y"] = xcheck_image(gold[f"{case}/x"][0])[None]
+    out["versions"] = np.array([f"torch {torch.__version__}", f"torchaudio {torchaudio.__version__}", f"numpy {np.__version__}"])
+    path = os.path.join(HERE, "melspec_xcheck.npz")
+    np.savez_compressed(path, **out)
+    for case in ("clean", "nan", "range"):
+        print(case, "xcheck vs oracle golden: max abs diff", float(np.abs(out[f"{case}/y"] - gold[f"{case}/y"]).max()))
+    print("wrote", path, os.path.getsize(path), "bytes")
+
+
 if __name__ == "__main__":
     if not rx.reference_available():
         raise SystemExit("/root/reference is not mounted: golden vectors can only be made in the build container")
-    make_stft()
-    make_melspec()
-    make_eegtransform()
+    only = set(sys.argv[1:])
+    for fn in (make_stft, make_melspec, make_eegtransform, make_fronthalf, make_melspec_xcheck):
+        if not only or fn.__name__ in only:
+            fn()

@@ -37,6 +37,15 @@ def test_against_golden(melspec_golden, case, key, mode, engine):
 
 
 @pytest.mark.parametrize("engine", ENGINES)
+@pytest.mark.parametrize("case", ["clean", "nan", "range"])
+def test_against_independent_torchaudio_image(melspec_golden, melspec_xcheck, case, engine):
+    """The CUDA path against the image torchaudio's library code produces (no oracle code involved)."""
+    got = run(melspec_golden[f"{case}/x"], engine=engine)
+    err = np.abs(got - melspec_xcheck[f"{case}/y"]).max()
+    assert err <= ATOL, f"{case}: max abs err {err:.3e}"
+
+
+@pytest.mark.parametrize("engine", ENGINES)
 def test_against_oracle_batch(engine):
     rng = np.random.default_rng(21)
     x = eeg_like(rng, (5, 20, 10000))

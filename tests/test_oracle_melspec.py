@@ -31,6 +31,63 @@ def test_crop_and_nan_fill_follow_reference_idiom():
     np.testing.assert_array_equal(mo.fill_missing(np.full(5, np.nan, np.float32)), np.zeros(5, np.float32))
 
 
+def test_front_half_against_the_references_own_functions(fronthalf_golden):
+    """``crop_offset`` / ``fill_missing`` / ``montage_differences`` against golden vectors produced by the
+    reference's own ``_get_eeg_window`` (cfg_utils.py:354-389, run on a parquet file) and
+    ``calculate_differential_signals`` (data_utils.py:183-215), lifted by ``oracle/ref_extract.py``."""
+    g = fronthalf_golden
+    for case in ("odd", "longodd"):
+        x = g[f"window/{case}/x"]                                  # (n_pts, 20) parquet rows, EEG_COLUMNS order
+        off = mo.crop_offset(x.shape[0])
+        for variant in ("full19", "magic8"):
+            want = g[f"window/{case}/{variant}"]
+            cols = [mo.EEG_COLUMNS.index(c) for c in g[f"channels/{variant}"]]
+            with np.errstate(all="ignore"):
+                import warnings
+                with warnings.catch_warnings():
+                    warnings.simplefilter("ignore")
+                    got = np.stack([mo.fill_missing(x[off:off + mo.EEG_PTS, c]) for c in cols], axis=1)
+            assert want.shape == (mo.EEG_PTS, len(cols)) and want.dtype == np.float32
+            np.testing.assert_array_equal(got, want)                # bit for bit, NaN-free
+    x = g["diff/x"]
+    want = g["diff/eeg_columns"]
+    np.testing.assert_array_equal(want[:20], x)
+    got = mo.montage_differences(x, mo.pair_indices(18))
+    np.testing.assert_array_equal(got, want[20:].astype(np.float32))   # integer microvolts: exact in fp32
+    want19 = g["diff/yaml_features"]                                # the YAML's own feature_to_index (19 channels)
+    assert list(g["diff/yaml_feature_names"]) == mo.EEG_COLUMNS[:19]
+    np.testing.assert_array_equal(want19[19:], want[20:])
+
+
+@pytest.mark.skipif(not rx.reference_available(), reason="/root/reference not mounted")
+def test_front_half_against_the_live_reference(tmp_path):
+    import pandas as pd
+
+    rng = np.random.default_rng(77)
+    x = eeg_like(rng, (11111, 20))
+    x[rng.random(11111) < 0.02, 6] = np.nan
+    x[:, 10] = np.nan
+    path = tmp_path / "eeg.parquet"
+    pd.DataFrame(x, columns=mo.EEG_COLUMNS).to_parquet(path)
+    fn, cfg = rx.load_reference_get_eeg_window()
+    import warnings
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        want = fn(path)
+        off = mo.crop_offset(11111)
+        got = np.stack([mo.fill_missing(x[off:off + 10000, mo.EEG_COLUMNS.index(c)]) for c in cfg.channel_feats], 1)
+    np.testing.assert_array_equal(got, want)
+
+
+def test_oracle_against_independent_torchaudio_image(melspec_golden, melspec_xcheck):
+    """A second implementation of the whole mode-N image from LIBRARY code (torchaudio MelSpectrogram +
+    amplitude_to_DB; ``tests/golden/make_golden.py::xcheck_image``).  Narrows, does not close, "unpinned"."""
+    for case in ("clean", "nan", "range"):
+        got = mo.eeg_to_spectrogram_batch_oracle(melspec_golden[f"{case}/x"])
+        err = np.abs(got - melspec_xcheck[f"{case}/y"]).max()
+        assert err <= 2e-5, f"{case}: {err:.2e}"
+
+
 def test_filterbank_structure_and_torchaudio():
     fb = mo.mel_filterbank()
     nz = np.argwhere(fb > 0)
