@@ -20,7 +20,7 @@ LIB_PATH = os.path.join(LIB_DIR, "libeegspec.so")
 STAMP = os.path.join(LIB_DIR, "libeegspec.stamp")
 INCLUDE = os.path.join(os.path.dirname(PKG_DIR), "include")
 
-SOURCES = ["abi.cu", "stft_image.cu", "melspec.cu", "melspec_tc.cu", "melspec_chain.cu", "melspec_roles.cu", "melspec_ts.cu", "eegtransform.cu"]
+SOURCES = ["abi.cu", "stft_image.cu", "melspec.cu", "melspec_tc.cu", "melspec_ts.cu", "eegtransform.cu"]
 NVCC_FLAGS = [
     "-O3", "-std=c++17",
     "-gencode", "arch=compute_100a,code=sm_100a",
@@ -52,8 +52,13 @@ def _headers():
         [os.path.join(INCLUDE, "eegspec.h")]
 
 
+def _defines():
+    """Extra -D flags for debug builds (tools only), e.g. EEGSPEC_BUILD_DEFINES=EEGSPEC_TIMELINE."""
+    return ["-D" + d for d in os.environ.get("EEGSPEC_BUILD_DEFINES", "").split(",") if d]
+
+
 def _fingerprint() -> str:
-    return _sha([os.path.join(CSRC, s) for s in SOURCES] + _headers())
+    return _sha([os.path.join(CSRC, s) for s in SOURCES] + _headers(), " ".join(_defines()).encode())
 
 
 def build(force: bool = False, verbose: bool = False) -> str:
@@ -77,12 +82,12 @@ def build(force: bool = False, verbose: bool = False) -> str:
     def compile_one(src: str):
         obj = os.path.join(obj_dir, src[:-3] + ".o")
         stamp = obj + ".stamp"
-        want = _sha([os.path.join(CSRC, src)] + hdrs)
+        want = _sha([os.path.join(CSRC, src)] + hdrs, " ".join(_defines()).encode())
         if not force and os.path.exists(obj) and os.path.exists(stamp):
             with open(stamp) as fh:
                 if fh.read().strip() == want:
                     return obj, ""
-        cmd = [_nvcc(), *compile_flags, "-I", INCLUDE, "-c"]
+        cmd = [_nvcc(), *compile_flags, *_defines(), "-I", INCLUDE, "-c"]
         if verbose:
             cmd += ["-Xptxas", "-v"]
         cmd += ["-o", obj, os.path.join(CSRC, src)]

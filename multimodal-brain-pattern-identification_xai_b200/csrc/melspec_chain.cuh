@@ -1,6 +1,6 @@
-// Shared pieces of the mode-N engine-3 kernels (melspec_chain.cu, melspec_roles.cu): geometry
-// constants, the argument block and the PTX wrappers (tcgen05 / TMEM, mbarrier, bulk copy,
-// cluster / DSMEM).
+// Shared pieces of the mode-N engine-3 kernel (melspec_ts.cu; eegtransform.cu borrows the PTX
+// wrappers): geometry constants, the argument block and the PTX wrappers (tcgen05 / TMEM, mbarrier,
+// bulk copy, cluster / DSMEM).
 #pragma once
 #include <cuda_fp16.h>
 
@@ -34,9 +34,9 @@ struct ChainArgs {
   int seg_lo[2], seg_n[2];     // staged sample range of each half (multiples of 4)
   float log2_amin, top_log2, out_bias, out_gain;
   int pair_a[EEGSPEC_MAX_PAIRS], pair_b[EEGSPEC_MAX_PAIRS];
-  long long* tl;               // debug timeline (EEGSPEC_TIMELINE), normally null
+  long long* tl;               // debug timeline (builds with -DEEGSPEC_TIMELINE only), normally null
   int tl_j0;
-  unsigned int stagger_ns;     // melspec_ts.cu: start delay per quarter-chain of stagger
+  unsigned int stagger_ns;     // start delay per quarter-chain of stagger
 };
 
 // ------------------------------------------------------------------------------ PTX helpers
@@ -220,8 +220,6 @@ __device__ __forceinline__ void c_named_bar(int id, int threads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
 }
 
-// melspec_roles.cu: the role-split variant of the engine-3 kernel (the default).
-int melspec_roles_run(const ChainArgs& a, long long clusters, cudaStream_t st);
 // melspec_ts.cu: frame operand in tensor memory, work item = record (a.n_items = records).
 int melspec_ts_run(const ChainArgs& a, long long clusters, cudaStream_t st);
 

@@ -56,7 +56,7 @@ int melspec_tc_launch_pair(const MelArgs& a, int n_pairs, long long n_records, c
 constexpr int kTcTableHalves = 4 * 112 * kFold;
 void melspec_tc_build_tables(const double* cos_d, const double* sin_d, int n_bins, unsigned short* out);
 
-// Engine 3 (melspec_chain.cu): persistent clustered kernel, no scratch.
+// Engine 3 (melspec_ts.cu): persistent clustered kernel, no scratch.
 bool melspec_chain_bank_matches(const eegspec_mel_params& p, int k_lo, const int* k0, const float* w0,
                                 const float* w1);
 int melspec_chain_launch(const MelArgs& m, const eegspec_mel_params& p, long long batch, cudaStream_t st);

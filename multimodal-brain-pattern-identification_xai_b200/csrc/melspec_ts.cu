@@ -3,11 +3,11 @@
 //
 // Why: with both operands in shared memory an M = 128, K = 16 tcgen05.mma costs ~126 cycles for
 // any N <= 128 (the 4 KB frame operand is read at ~32 B/clk; tools/mma_probe.cu), so the 24 MMAs
-// of a tile took 3 000 cycles and the tensor pipe was the bottleneck of the role-split kernel
-// (melspec_roles.cu) at 15 % "active".  With the frame operand in tensor memory the same MMA
+// of a tile took 3 000 cycles and the tensor pipe was the bottleneck of the earlier role-split
+// kernel (git history) at 15 % "active".  With the frame operand in tensor memory the same MMA
 // runs at its N / 2 floor (59 cycles at N = 112, tools/mma_probe2.cu).
 //
-// Same arithmetic as melspec_roles.cu (folded 128-sample Hann frame, split-fp16 operands, fp32
+// Arithmetic: folded 128-sample Hann frame, split-fp16 operands, fp32
 // TMEM accumulators, |X|^2 -> 2-tap mel -> lg2, deferred clip of the pair image with the maximum
 // exchanged between the two CTAs of the cluster, log values parked in tensor memory), and:
 //
@@ -31,10 +31,16 @@
 // Front half follows the reference (pair list /root/reference/root/config/config.yml:529-545,
 // differencing /root/reference/root/src/utils/data_utils.py:183-215, crop
 // /root/reference/root/src/utils/cfg_utils.py:369-371, NaN fill cfg_utils.py:380-385).
+#ifdef EEGSPEC_TIMELINE   // debug builds only (tools/timeline_roles.py): clock stamps of the pipeline hand-offs
 #include <stdio.h>
 #include <stdlib.h>
 
 #include <vector>
+#endif
+
+#include <math.h>
+
+#include <mutex>
 
 #include "mel_default_epilogue.h"
 #include "melspec_chain.cuh"
@@ -53,7 +59,7 @@ constexpr int kTMmaWarp = kTEpiWarps + kTBuildWarps, kTLoadWarp = kTMmaWarp + 1,
 constexpr int kTDiff = 64;   // two difference warps
 constexpr int kTThreads = kTEpi + kTBuild + 128;
 constexpr int kTYFloats = kCStageFloats + 2 * kCMargin + 128;
-constexpr int kTlTilesT = 64, kTlSlotsT = 32;
+constexpr int kTlTilesT = 64, kTlSlotsT = 40;
 constexpr uint32_t kTIdesc = (1u << 4) | ((uint32_t)(kTBins >> 3) << 17) | ((uint32_t)(kTileFrames >> 4) << 24);
 constexpr uint32_t kTIdescX = (1u << 4) | ((uint32_t)(kTXN >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
 
@@ -129,13 +135,33 @@ __device__ __forceinline__ float t_ord2f(unsigned int u) {
 // Asynchronous 4-byte store into the peer CTA's shared memory that completes 4 transaction bytes
 // on the peer's mbarrier at the same offset as `local_bar`: data and signal travel together, no
 // cluster-scope release fence (which is a MEMBAR.ALL.GPU waiting on every store in flight).
-__device__ __forceinline__ void t_st_async_peer(uint32_t local_addr, uint32_t local_bar, uint32_t peer_rank, float v) {
-  uint32_t raddr, rbar;
-  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(raddr) : "r"(local_addr), "r"(peer_rank));
-  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(rbar) : "r"(local_bar), "r"(peer_rank));
+__device__ __forceinline__ uint32_t t_mapa(uint32_t local_addr, uint32_t peer_rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local_addr), "r"(peer_rank));
+  return r;
+}
+// raddr / rbar: shared::cluster addresses in the peer CTA (t_mapa, computed once)
+__device__ __forceinline__ void t_st_async_peer(uint32_t raddr, uint32_t rbar, float v) {
   asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.b32 [%0], %1, [%2];" ::"r"(raddr),
                "r"(__float_as_uint(v)), "r"(rbar)
                : "memory");
+}
+
+// Wait with an explicit back-off.  c_mbar_wait compiles to TRYWAIT / NANOSLEEP.SYNCS / PHASECHK / BRA and
+// a waiting warp goes round that loop every ~20 ns: sixteen epilogue warps in the exchange wait and eight
+// build warps waiting for a ring slot executed 40 % of the kernel's warp instructions there.
+__device__ __forceinline__ void t_mbar_wait_sleep(uint32_t bar, uint32_t parity, uint32_t ns) {
+  asm volatile(
+      "{\n\t.reg .pred P1;\n\t"
+      "TW_%=:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1, %2;\n\t"
+      "@P1 bra TD_%=;\n\t"
+      "nanosleep.u32 %3;\n\t"
+      "bra TW_%=;\n\t"
+      "TD_%=:\n\t}\n"
+      :
+      : "r"(bar), "r"(parity), "r"(0x989680u), "r"(ns)
+      : "memory");
 }
 
 template <bool kTimeline>
@@ -153,7 +179,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTThreads, 1) melspe
   const int cluster_id = blockIdx.x >> 1, n_clusters = gridDim.x >> 1;
   const int n_items = (int)a.n_items;   // records
   const int n_my_items = n_items > cluster_id ? (n_items - cluster_id + n_clusters - 1) / n_clusters : 0;
-  const int tpi = a.ppc * a.n_chains;   // tiles per item (16)
+  // geometry this kernel is launched for (melspec_ts_run checks it): literals, not runtime divisors
+  constexpr int kPpc = 4, tpi = 16, kNMels = 128, kNTime = 2 * kTileFrames;   // tiles per item = 4 chains x 4 pairs
   const int J = n_my_items * tpi;
   if (J == 0) return;   // both CTAs of the cluster agree
 #define TL(slot)                                                                                             \
@@ -238,7 +265,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTThreads, 1) melspe
     const int q = j / tpi;
     rec = cluster_id + q * n_clusters;
     const int k = j - q * tpi;
-    return ((k + rot * a.ppc) & (tpi - 1));   // tpi = 16
+    return ((k + rot * kPpc) & (tpi - 1));
   };
 
   // ======================================================================= single-lane roles
@@ -259,17 +286,33 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTThreads, 1) melspe
 #pragma unroll
         for (int ks = 0; ks < kFold / 16; ++ks) tlo[t][ks] = dlo(tab0 + t * kCTabBytes + ks * 256);
       const bool leader = t_elect_one();
+      bool seen_prev = true;
+      auto observe = [&](int j, int where) {   // timeline only: when does the MMA warp first see tile j - 1 complete?
+        if (!kTimeline || seen_prev || j < 1) return;
+        uint32_t ok;
+        asm volatile("{\n\t.reg .pred P1;\n\tmbarrier.test_wait.parity.shared::cta.b64 P1, [%1], %2;\n\tselp.u32 %0, 1, 0, P1;\n\t}\n"
+                     : "=r"(ok) : "r"(mma_bar0 + 8 * ((j - 1) & 1)), "r"((uint32_t)(((j - 1) >> 1) & 1)) : "memory");
+        if (ok) {
+          seen_prev = true;
+          const int jj = j;
+          { const int j = jj - 1; TL(32); if (blockIdx.x < 2 && lane == 0 && j >= a.tl_j0 && j < a.tl_j0 + kTlTilesT) a.tl[((blockIdx.x * kTlTilesT + (j - a.tl_j0)) * kTlSlotsT) + 33] = where; }
+        }
+      };
       for (int j = 0; j < J; ++j) {
         const uint32_t d_re = tmem_base + (j & 1) * kTAcc, d_im = d_re + kTBins;
+        seen_prev = false;
+        observe(j, 0);
 #pragma unroll
         for (int ks = 0; ks < kFold / 16; ++ks) {
           constexpr int dummy = 0; (void)dummy;
           const int slot = ks & 1;                                  // (4 j + ks) & 1
           c_mbar_wait(ops_bar0 + 8 * slot, (uint32_t)(ks >> 1));    // ((4 j + ks) >> 1) & 1
+          observe(j, 1 + 2 * ks);
           if (ks == 0) {
             TL(5);
             if (j >= 2) c_mbar_wait(tmem_free0 + 8 * (j & 1), ((j - 2) >> 1) & 1);
             TL(6);
+            observe(j, 10);
           }
           TL(24 + ks);
           asm volatile("tcgen05.fence::after_thread_sync;" ::);
@@ -300,6 +343,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTThreads, 1) melspe
           }
           __syncwarp();
           TL(28 + ks);
+          observe(j, 2 + 2 * ks);
         }
         TL(7);
       }
@@ -466,7 +510,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTThreads, 1) melspe
           if (lane == 0) c_mbar_arrive(y_free0 + 8 * (j & 1));
         }
         if (ks >= 2 && bwarp == 0) TL(16 + 4 * (ks - 2));
-        if (g >= 2) c_mbar_wait(afree0 + 8 * slot, (uint32_t)(((ks >> 1) + 1) & 1));   // ((g - 2) >> 1) & 1: the MMAs of step g - 2 have read the slot
+        if (g >= 2) t_mbar_wait_sleep(afree0 + 8 * slot, (uint32_t)(((ks >> 1) + 1) & 1), 32);   // ((g - 2) >> 1) & 1: the MMAs of step g - 2 have read the slot
         if (ks == 0 && bwarp == 0) TL(3);
         if (ks >= 2 && bwarp == 0) TL(17 + 4 * (ks - 2));
         asm volatile("tcgen05.fence::after_thread_sync;" ::);
@@ -510,6 +554,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTThreads, 1) melspe
     static_assert(MELGEN_COL0_P4_2 == 2 * MELGEN_COL0_P4_1 && MELGEN_COL0_P4_3 == 3 * MELGEN_COL0_P4_1, "part pitch");
     auto park_col = [](int g) { return (uint32_t)(8 * (1 + g / 2) + (g & 1) * kTBins); };
     const uint32_t lane_base = tmem_base + ((uint32_t)(32 * (warp & 3)) << 16);
+    const uint32_t peer_pv0 = t_mapa(c_smem_u32(&sh.pv[0][warp]), (uint32_t)peer), peer_xch0 = t_mapa(xch_bar0, (uint32_t)peer);
     float acc[kTMels];
 #pragma unroll
     for (int i = 0; i < kTMels; ++i) acc[i] = 0.f;
@@ -519,7 +564,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTThreads, 1) melspe
     // exchange n is complete: fold the parked log values of tile n into the chain sum with the
     // pair's clip level, then hand accumulator buffer n & 1 back to the MMA warp.
     auto fold_tile = [&](int n) {
-      c_mbar_wait(xch_bar0 + 8 * (n & 1), (uint32_t)((n >> 1) & 1));
+      t_mbar_wait_sleep(xch_bar0 + 8 * (n & 1), (uint32_t)((n >> 1) & 1), 64);
       { const int j = n; if (warp == 0) TL(9); }
       float r_pair = fmaxf(t_ord2f(sh.xmax[n & 3]), a.log2_amin);
       {
@@ -549,9 +594,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTThreads, 1) melspe
     // Output rows of this thread: mel rows [32 part, 32 part + 32) of the record, frames of this
     // half: one 2 KB segment (128 frames x 4 chains) per mel row.
     auto row_seg = [&](int rec) {
-      return a.out + (((long long)rec * a.n_mels + kTMels * part) * a.n_time + 128 * h) * 4;
+      return a.out + (((long long)rec * kNMels + kTMels * part) * kNTime + 128 * h) * 4;
     };
-    const long long mstride = (long long)a.n_time * 4;
+    constexpr long long mstride = (long long)kNTime * 4;
     // The chain whose last tile is j_last is complete.  It is stashed in the record's own output
     // rows, blocked so that every store is a full-line 16-byte-per-lane store: the segment of
     // row 4 g + c holds, for chain c, [frame][mels 4 g .. 4 g + 3] (L2 resident until the
@@ -559,7 +604,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTThreads, 1) melspe
     auto chain_done = [&](int j_last) {
       int rec;
       const int pr = pair_of(j_last, rec);
-      float* o = row_seg(rec) + (pr / a.ppc) * mstride + 4 * t_frame;
+      float* o = row_seg(rec) + (pr / kPpc) * mstride + 4 * t_frame;
 #pragma unroll
       for (int g = 0; g < kTMels / 4; ++g) {
         float4 v;
@@ -664,7 +709,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTThreads, 1) melspe
         const float v = c_lg2(vmax) - 2.f * (float)e_j;
         const uint32_t xb = xch_bar0 + 8 * (j & 1);
         atomicMax(&sh.xmax[j & 3], t_f2ord(v));
-        t_st_async_peer(c_smem_u32(&sh.pv[j & 1][warp]), xb, (uint32_t)peer, v);
+        t_st_async_peer(peer_pv0 + (j & 1) * (uint32_t)sizeof(sh.pv[0]), peer_xch0 + 8 * (j & 1), v);
         if (warp == 0) c_mbar_expect_tx(xb, 4 * kTEpiWarps);
         else c_mbar_arrive(xb);
       }
@@ -681,7 +726,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTThreads, 1) melspe
       // The chain that ended with tile j - 1 is stashed HERE, inside the exchange wait of tile j: its
       // 64 KB of stores per CTA run into the SM's store throttle (~1 100 ns) and would sit on the
       // critical path at the end of tile j - 1; the accumulators are not touched before fold j.
-      if (j > 0 && j % a.ppc == 0) {
+      if (j > 0 && j % kPpc == 0) {
         chain_done(j - 1);
 #pragma unroll
         for (int i = 0; i < kTMels; ++i) acc[i] = 0.f;
@@ -719,43 +764,126 @@ size_t melspec_ts_smem_bytes() {
 
 // Launches the TS kernel on `clusters` clusters of two CTAs; `a.n_items` must be the number of
 // RECORDS (the kernel walks all chains of a record).  Geometry checks are the caller's
-// (melspec_chain_launch); this form additionally needs 4 chains of 4 pairs and 128 mels.
+// (melspec_chain_launch, below); this form needs 4 chains of 4 pairs, 128 mels and 256 kept frames.
 int melspec_ts_run(const ChainArgs& a, long long clusters, cudaStream_t st) {
-  if (a.n_chains != 4 || a.ppc != 4 || a.n_mels != 128) return EEGSPEC_EUNSUPPORTED;
+  if (a.n_chains != 4 || a.ppc != 4 || a.n_mels != 128 || a.n_time != 2 * kTileFrames) return EEGSPEC_EUNSUPPORTED;
+  static std::mutex mu;
   static bool configured[64] = {};
   int dev = 0;
   cudaGetDevice(&dev);
   if (dev < 0 || dev >= 64) return EEGSPEC_EUNSUPPORTED;
   const size_t smem = melspec_ts_smem_bytes();
+  std::lock_guard<std::mutex> lock(mu);
   if (!configured[dev]) {
     cudaError_t e = cudaFuncSetAttribute(melspec_ts_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return (int)e;
+#ifdef EEGSPEC_TIMELINE
     e = cudaFuncSetAttribute(melspec_ts_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return (int)e;
+#endif
     configured[dev] = true;
   }
-  // EEGSPEC_TIMELINE=<file>: debug only -- synchronous launch that dumps clock stamps of the
-  // pipeline hand-offs of CTAs 0 and 1 (64 tiles from EEGSPEC_TIMELINE_J0) as raw int64
-  // (%globaltimer nanoseconds, comparable between the two CTAs).
-  const char* tl_path = getenv("EEGSPEC_TIMELINE");
-  ChainArgs b = a;
-  const size_t tl_bytes = sizeof(long long) * 2 * kTlTilesT * kTlSlotsT;
-  if (tl_path) {
+#ifdef EEGSPEC_TIMELINE
+  // EEGSPEC_TIMELINE=<file>: synchronous launch that dumps clock stamps of the pipeline hand-offs of
+  // CTAs 0 and 1 (64 tiles from EEGSPEC_TIMELINE_J0) as raw int64 (%globaltimer nanoseconds).
+  if (const char* tl_path = getenv("EEGSPEC_TIMELINE")) {
+    ChainArgs b = a;
+    const size_t tl_bytes = sizeof(long long) * 2 * kTlTilesT * kTlSlotsT;
     const char* j0 = getenv("EEGSPEC_TIMELINE_J0");
     b.tl_j0 = j0 ? atoi(j0) : 0;
     if (cudaMalloc(&b.tl, tl_bytes) != cudaSuccess) return EEGSPEC_EWORKSPACE;
     cudaMemsetAsync(b.tl, 0, tl_bytes, st);
-  }
-  if (tl_path) melspec_ts_kernel<true><<<(unsigned)(2 * clusters), kTThreads, smem, st>>>(b);
-  else melspec_ts_kernel<false><<<(unsigned)(2 * clusters), kTThreads, smem, st>>>(b);
-  if (tl_path) {
+    melspec_ts_kernel<true><<<(unsigned)(2 * clusters), kTThreads, smem, st>>>(b);
     std::vector<long long> hbuf(2 * kTlTilesT * kTlSlotsT);
     cudaStreamSynchronize(st);
     cudaMemcpy(hbuf.data(), b.tl, tl_bytes, cudaMemcpyDeviceToHost);
     cudaFree(b.tl);
     if (FILE* f = fopen(tl_path, "wb")) { fwrite(hbuf.data(), 1, tl_bytes, f); fclose(f); }
+    return (int)cudaGetLastError();
   }
+#endif
+  melspec_ts_kernel<false><<<(unsigned)(2 * clusters), kTThreads, smem, st>>>(a);
   return (int)cudaGetLastError();
+}
+
+// The generated epilogue is only valid for the bank it was generated from.
+bool melspec_chain_bank_matches(const eegspec_mel_params& p, int k_lo, const int* k0, const float* w0,
+                                const float* w1) {
+  if (p.sr != MELGEN_SR || p.n_fft != MELGEN_NFFT || p.n_mels != MELGEN_NMELS || k_lo != MELGEN_KLO) return false;
+  for (int m = 0; m < MELGEN_NMELS; ++m) {
+    if (k0[m] != kGenK0[m]) return false;
+    if (fabsf(w0[m] - kGenW0[m]) > 2e-6f * fabsf(kGenW0[m])) return false;
+    if (fabsf(w1[m] - kGenW1[m]) > 2e-6f * fabsf(kGenW1[m]) + 1e-12f) return false;
+  }
+  return true;
+}
+
+// Returns EEGSPEC_EUNSUPPORTED when this geometry / layout is not served by engine 3.
+int melspec_chain_launch(const MelArgs& m, const eegspec_mel_params& p, long long batch, cudaStream_t st) {
+  if (p.time_major || m.n_time != 2 * kTileFrames || m.n_frames < m.n_time) return EEGSPEC_EUNSUPPORTED;
+  if (m.n_frames - m.n_time > kCMaxExtra || m.hop > 40 || m.hop < 1 || (m.crop & 7)) return EEGSPEC_EUNSUPPORTED;
+  if ((reinterpret_cast<uintptr_t>(m.eeg) & 15) || (m.rec_stride & 3) || (m.ch_stride & 3) || (m.crop_off & 3))
+    return EEGSPEC_EUNSUPPORTED;
+  ChainArgs a;
+  a.tl = nullptr;
+  a.tl_j0 = 0;
+  a.eeg = m.eeg;
+  a.out = m.out;
+  a.tab = m.t.tc3_tab;
+  a.mel_k0 = m.t.mel_k0;
+  a.mel_w0 = m.t.mel_w0;
+  a.mel_w1 = m.t.mel_w1;
+  a.rec_stride = m.rec_stride;
+  a.ch_stride = m.ch_stride;
+  a.n_items = batch * m.n_chains;
+  a.crop = m.crop;
+  a.crop_off = m.crop_off;
+  a.hop = m.hop;
+  a.n_frames = m.n_frames;
+  a.n_mels = m.n_mels;
+  a.n_time = m.n_time;
+  a.n_chains = m.n_chains;
+  a.ppc = m.ppc;
+  a.pad_mode = m.pad_mode;
+  const int last = (m.n_frames < m.n_time + kCMaxExtra ? m.n_frames : m.n_time + kCMaxExtra) - 1;
+  auto up4 = [](int v) { return (v + 3) & ~3; };
+  a.seg_lo[0] = 0;
+  a.seg_n[0] = (up4((kTileFrames - 1) * m.hop + 64) < m.crop ? up4((kTileFrames - 1) * m.hop + 64) : m.crop);
+  a.seg_lo[1] = (kTileFrames * m.hop - 63) & ~3;
+  const int hi1 = up4(last * m.hop + 64) < m.crop ? up4(last * m.hop + 64) : m.crop;
+  a.seg_n[1] = hi1 - a.seg_lo[1];
+  for (int h = 0; h < 2; ++h)
+    if (a.seg_n[h] <= 0 || a.seg_n[h] > kCStageFloats || a.seg_lo[h] < 0) return EEGSPEC_EUNSUPPORTED;
+  if (a.seg_lo[1] + a.seg_n[1] < m.crop && last * m.hop + 64 > a.seg_lo[1] + a.seg_n[1]) return EEGSPEC_EUNSUPPORTED;
+  a.log2_amin = log2f(m.amin);
+  a.top_log2 = m.top_db / kLog2To10Log10;
+  a.out_bias = m.db_offset * m.inv_db_scale;
+  a.out_gain = kLog2To10Log10 * m.inv_db_scale / (float)m.ppc;
+  for (int i = 0; i < EEGSPEC_MAX_PAIRS; ++i) { a.pair_a[i] = m.pair_a[i]; a.pair_b[i] = m.pair_b[i]; }
+
+  static std::mutex mu;
+  static int sm_count[64] = {};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 0 || dev >= 64) return EEGSPEC_EUNSUPPORTED;
+  {
+    std::lock_guard<std::mutex> lock(mu);
+    if (!sm_count[dev]) {
+      const cudaError_t e = cudaDeviceGetAttribute(&sm_count[dev], cudaDevAttrMultiProcessorCount, dev);
+      if (e != cudaSuccess) return (int)e;
+    }
+  }
+  if (a.n_chains != 4 || a.ppc != 4 || a.n_mels != 128) return EEGSPEC_EUNSUPPORTED;
+  // work item = record: one cluster of two CTAs per SM pair walks records cluster_id, cluster_id + n, ...
+  a.n_items = batch;
+  a.stagger_ns = 2500;   // start delay per quarter chain: spreads the clusters' stash bursts
+  long long clusters = sm_count[dev] / 2;
+  if (clusters < 1) clusters = 1;
+  if (clusters > batch) clusters = batch;
+  if ((batch + clusters - 1) / clusters * 16 > (1LL << 28)) return EEGSPEC_EUNSUPPORTED;
+  const int rc = melspec_ts_run(a, clusters, st);
+  if (rc == 0) count_launch();
+  return rc;
 }
 
 }  // namespace eegspec

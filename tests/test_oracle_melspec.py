@@ -143,3 +143,5 @@ def test_generated_mel_epilogue_is_current_and_matches_the_bank():
     spec.loader.exec_module(gen)
     with open(gen.OUT) as fh:
         assert fh.read() == gen.render()
+    # the generator derives the bank itself (product-side derivation); it must be the oracle's bank
+    np.testing.assert_array_equal(gen.bank(), mo.mel_filterbank())
