@@ -119,7 +119,15 @@ void eegspec_mel_params_default(eegspec_mel_params *p);
 /* Output geometry for these parameters: frames per pair and kept time columns. */
 int eegspec_melspec_geometry(const eegspec_mel_params *p, int32_t *n_frames, int32_t *n_time);
 
+/* Scratch bytes that serve EVERY engine for `batch` records (the generic engines 1 / 2 keep
+ * 16 x n_mels x n_time fp32 per record for up to 256 records at a time). */
 size_t eegspec_melspec_workspace(int64_t batch, const eegspec_mel_params *p);
+
+/* Scratch bytes the DEFAULT engine needs when it serves the geometry: 0 for channel-major records,
+ * the gathered electrode rows of one pass for time-major ones.  A call that turns out to need more
+ * (a geometry only the generic engines serve) returns EEGSPEC_EWORKSPACE and changes nothing; the
+ * caller then retries with eegspec_melspec_workspace() bytes. */
+size_t eegspec_melspec_workspace_default(int64_t batch, const eegspec_mel_params *p);
 
 /* eeg: device fp32, `batch` records `rec_stride` elements apart, each n_ch x length
  * (or length x n_ch when time_major).  out: device (batch, n_mels, n_time, n_chains) fp32. */

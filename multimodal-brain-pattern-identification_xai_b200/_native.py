@@ -64,6 +64,7 @@ SIGNATURES = {
     "eegspec_melspec_geometry": (C.c_int, [C.POINTER(MelParams), C.POINTER(C.c_int32),
                                            C.POINTER(C.c_int32)]),
     "eegspec_melspec_workspace": (C.c_size_t, [C.c_int64, C.POINTER(MelParams)]),
+    "eegspec_melspec_workspace_default": (C.c_size_t, [C.c_int64, C.POINTER(MelParams)]),
     "eegspec_melspec_f32": (C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_int64, C.c_int64,
                                       C.POINTER(MelParams), C.c_void_p, C.c_void_p, C.c_size_t,
                                       C.c_void_p]),

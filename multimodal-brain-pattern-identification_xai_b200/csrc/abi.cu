@@ -169,6 +169,10 @@ size_t eegspec_melspec_workspace(int64_t batch, const eegspec_mel_params* p) {
   return melspec_workspace(batch, p);
 }
 
+size_t eegspec_melspec_workspace_default(int64_t batch, const eegspec_mel_params* p) {
+  return melspec_workspace_default(batch, p);
+}
+
 int eegspec_melspec_f32(const float* eeg, int64_t batch, int32_t n_ch, int64_t length,
                         int64_t rec_stride, const eegspec_mel_params* p, float* out,
                         void* workspace, size_t workspace_bytes, void* stream) {

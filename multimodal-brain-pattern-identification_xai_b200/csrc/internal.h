@@ -29,6 +29,7 @@ struct MelGeometry {
 };
 int melspec_geometry(const eegspec_mel_params* p, MelGeometry* g);
 size_t melspec_workspace(long long batch, const eegspec_mel_params* p);
+size_t melspec_workspace_default(long long batch, const eegspec_mel_params* p);
 int melspec_launch(const float* eeg, long long batch, int n_ch, long long length,
                    long long rec_stride, const eegspec_mel_params* p, float* out, void* workspace,
                    size_t workspace_bytes, cudaStream_t st);

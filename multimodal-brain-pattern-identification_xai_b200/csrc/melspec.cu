@@ -544,6 +544,12 @@ size_t melspec_workspace(long long batch, const eegspec_mel_params* p) {
   return need;
 }
 
+size_t melspec_workspace_default(long long batch, const eegspec_mel_params* p) {
+  MelGeometry g;
+  if (batch <= 0 || melspec_geometry(p, &g) != EEGSPEC_OK || !p->time_major) return 0;
+  return gather_scratch_per_record(*p) * (size_t)(batch < kGatherChunk ? batch : kGatherChunk);
+}
+
 static size_t pair_kernel_smem(const eegspec_mel_params& p) {
   size_t f = 0;
   f += 2 * (size_t)kFold * kBinGroups * kGroupPitch;   // cos, sin

@@ -42,7 +42,9 @@ def gather_spectrograms(local: torch.Tensor, n_records: int, group=None) -> torc
     out = torch.empty((world * biggest,) + tuple(local.shape[1:]), dtype=local.dtype,
                       device=local.device)
     dist.all_gather_into_tensor(out, padded.contiguous(), group=group)
-    parts = [out[r * biggest: r * biggest + (hi - lo)] for r, (lo, hi) in enumerate(sizes)]
+    if all(hi - lo == biggest for lo, hi in sizes):
+        return out                      # equal shards: the collective's buffer IS the result, no second copy
+    parts =[out[r * biggest: r * biggest + (hi - lo)] for r, (lo, hi) in enumerate(sizes)]
     return torch.cat(parts, dim=0)
 
 

@@ -169,12 +169,14 @@ def melspec_geometry(params: Optional[nat.MelParams] = None) -> tuple[int, int]:
 
 
 def eeg_to_spectrogram(eeg: torch.Tensor, params: Optional[nat.MelParams] = None,
-                       **kwargs) -> torch.Tensor:
+                       out: Optional[torch.Tensor] = None, **kwargs) -> torch.Tensor:
     """Raw EEG -> the 4-chain log-mel image of the multimodal model's spectrogram branch.
 
     ``eeg``: (B, 20, L>=10000) fp32, channels in ``montage.EEG_COLUMNS`` order (or (20, L) for one
     record; (B, L, 20) with ``time_major=True``, the parquet layout).  Returns
     (B, 128, 256, 4) fp32 -- (mel, time, chain) with chains LL, LP, RP, RR -- on ``eeg.device``.
+    ``out`` (device input only): a contiguous fp32 tensor of that shape to write into, e.g. a slice of
+    a dataset-sized buffer (the 107 k-segment set keeps its 56 GB of images resident that way).
     """
     _require_cuda()
     params = params if params is not None else mel_params(**kwargs)
@@ -192,19 +194,31 @@ def eeg_to_spectrogram(eeg: torch.Tensor, params: Optional[nat.MelParams] = None
     if batch == 0:
         return torch.empty(shape, dtype=torch.float32, device=eeg.device)
     if not x.is_cuda:
+        if out is not None:
+            raise ValueError("out= is only supported for device inputs")
         out = torch.empty(shape, dtype=torch.float32, pin_memory=True)
         nat.check(nat.lib.eegspec_melspec_host_f32(_ptr(x), batch, n_ch, length, C.byref(params),
                                                    _ptr(out), torch.cuda.current_device()),
                   "eeg_to_spectrogram")
     else:
         with torch.cuda.device(x.device):
-            out = torch.empty(shape, dtype=torch.float32, device=x.device)
-            ws_bytes = nat.lib.eegspec_melspec_workspace(batch, C.byref(params))
-            ws = torch.empty(ws_bytes, dtype=torch.uint8, device=x.device)
-            nat.check(nat.lib.eegspec_melspec_f32(_ptr(x), batch, n_ch, length, n_ch * length,
-                                                  C.byref(params), _ptr(out), _ptr(ws), ws_bytes,
-                                                  _stream_ptr(x.device)),
-                      "eeg_to_spectrogram")
+            if out is None:
+                out = torch.empty(shape, dtype=torch.float32, device=x.device)
+            elif (tuple(out.shape) != shape or out.dtype != torch.float32 or out.device != x.device
+                  or not out.is_contiguous()):
+                raise ValueError(f"out must be a contiguous fp32 tensor of shape {shape} on {x.device}")
+            # The default engine needs no scratch for channel-major records (only the row gather of
+            # time-major ones does): ask for the generic engines' 0.5 GiB only when the library says so.
+            ws_bytes = nat.lib.eegspec_melspec_workspace_default(batch, C.byref(params))
+            ws = torch.empty(ws_bytes, dtype=torch.uint8, device=x.device) if ws_bytes else None
+            rc = nat.lib.eegspec_melspec_f32(_ptr(x), batch, n_ch, length, n_ch * length, C.byref(params),
+                                             _ptr(out), _ptr(ws), ws_bytes, _stream_ptr(x.device))
+            if rc == nat.EWORKSPACE:
+                ws_bytes = nat.lib.eegspec_melspec_workspace(batch, C.byref(params))
+                ws = torch.empty(ws_bytes, dtype=torch.uint8, device=x.device)
+                rc = nat.lib.eegspec_melspec_f32(_ptr(x), batch, n_ch, length, n_ch * length, C.byref(params),
+                                                 _ptr(out), _ptr(ws), ws_bytes, _stream_ptr(x.device))
+            nat.check(rc, "eeg_to_spectrogram")
     return out[0] if single else out
 
 
@@ -244,11 +258,16 @@ def eeg_to_spectrogram_sliding(eeg: torch.Tensor, window: int = 10000, stride: i
     xd = x.contiguous().cuda(non_blocking=True) if on_host else x.contiguous()
     with torch.cuda.device(xd.device):
         out = torch.empty(shape, dtype=torch.float32, device=xd.device)
-        ws_bytes = nat.lib.eegspec_melspec_workspace(n_win, C.byref(params))
-        ws = torch.empty(ws_bytes, dtype=torch.uint8, device=xd.device)
-        nat.check(nat.lib.eegspec_melspec_sliding_f32(_ptr(xd), n_ch, total, stride, n_win, C.byref(params),
-                                                      _ptr(out), _ptr(ws), ws_bytes, _stream_ptr(xd.device)),
-                  "eeg_to_spectrogram_sliding")
+        ws_bytes = nat.lib.eegspec_melspec_workspace_default(n_win, C.byref(params))
+        ws = torch.empty(ws_bytes, dtype=torch.uint8, device=xd.device) if ws_bytes else None
+        rc = nat.lib.eegspec_melspec_sliding_f32(_ptr(xd), n_ch, total, stride, n_win, C.byref(params),
+                                                 _ptr(out), _ptr(ws), ws_bytes, _stream_ptr(xd.device))
+        if rc == nat.EWORKSPACE:        # a stride / geometry the default engine does not serve
+            ws_bytes = nat.lib.eegspec_melspec_workspace(n_win, C.byref(params))
+            ws = torch.empty(ws_bytes, dtype=torch.uint8, device=xd.device)
+            rc = nat.lib.eegspec_melspec_sliding_f32(_ptr(xd), n_ch, total, stride, n_win, C.byref(params),
+                                                     _ptr(out), _ptr(ws), ws_bytes, _stream_ptr(xd.device))
+        nat.check(rc, "eeg_to_spectrogram_sliding")
     if on_host:
         host = torch.empty(shape, dtype=torch.float32, pin_memory=True)
         host.copy_(out)
