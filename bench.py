@@ -661,8 +661,10 @@ def leg_eeg_transform(torch, b200spec, timed, keep, peak, world, args):
         def step_fused():
             keep["xf"] = b200spec.eeg_transform_stft(x19, Cfg, xf)
 
+        xf_cm = b200spec.EEGTransformer(n_feats=19, downsample=5, channel_major=True)
+
         def step_two():
-            keep["xf"] = b200spec.compute_stft(xf.transform(x19, channel_major=True), Cfg)
+            keep["xf"] = b200spec.compute_stft(xf_cm.transform(x19), Cfg)
 
         ms_f, _ = timed(step_fused, max(3, args.steps // 2), 3)
         ms_2, _ = timed(step_two, max(3, args.steps // 2), 3)
@@ -670,8 +672,9 @@ def leg_eeg_transform(torch, b200spec, timed, keep, peak, world, args):
         st = max(3, args.steps // 2)
         bytes_f = 4 * 10000 * 19 + 4 * 19 * 33 * 2000
         out["fused_stft"] = {
-            "what": "raw (B,10000,19) -> (B,19,33,2000) in one entry point: the 2000-sample rows stay on chip between the IIR "
-                    "and the STFT (dataset.py:73-104 -> DiffEEG_utils.py:27-76)",
+            "what": "raw (B,10000,19) -> (B,19,33,2000) in one entry point, eegspec_eeg_transform_stft_f32 (dataset.py:73-104 -> "
+                    "DiffEEG_utils.py:27-76): two launches, the 2000-sample rows (3 % of the bytes) in a workspace between them; "
+                    "L2-sized passes were measured slower (DESIGN.md)",
             "value": world * RECORDS * st / (ms_f * 1e-3), "unit": UNIT, "ms_per_step": ms_f / st,
             "two_kernel_ms_per_step": ms_2 / st,
             "roofline": roofline(RECORDS * bytes_f, ms_f * 1e-3 / st, peak, f"eeg_transform_stft, {bytes_f} B/record")}

@@ -201,11 +201,25 @@ void eegspec_xform_params_default(eegspec_xform_params *p);
 int64_t eegspec_xform_out_length(int64_t length, const eegspec_xform_params *p);
 
 /* x: device fp32, `batch` records of (length, n_ch) TIME-major (the reference's (L, C) arrays),
- * consecutive records `rec_stride` elements apart, 16-byte aligned, n_ch % 4 == 0.
+ * consecutive records `rec_stride` elements apart, 16-byte aligned, rec_stride % 4 == 0, and either
+ * n_ch % 4 == 0 or length % 4 == 0 (the reference's (10000, 19) windows qualify; else EEGSPEC_EALIGN).
  * out: device fp32 (batch, L_out, n_out) or (batch, n_out, L_out), see out_channel_major. */
 int eegspec_eeg_transform_f32(const float *x, int64_t batch, int64_t length, int32_t n_ch,
                               int64_t rec_stride, const eegspec_xform_params *p, float *out,
                               void *stream);
+
+/* Row (f)1 fused with the path: raw (batch, length, n_ch) time-major EEG -> the compute_stft image of
+ * the transformed signal, (batch, n_out, nperseg/2+1, out_cols) fp32 -- what
+ * compute_stft(EEGDataset[i]["x"]) produces in /root/reference/root/src/training/DiffEEG_train.py:128-131
+ * from the (C, 2000) rows dataset.py:213-228 hands out.  Two launches per pass of up to ~2 000 records; the
+ * transformed rows (n_out x L_out fp32 per record, 152 KB = 3 % of the image) live in the caller's
+ * workspace between them (eegspec_eeg_transform_stft_workspace() bytes). */
+size_t eegspec_eeg_transform_stft_workspace(int64_t batch, int64_t length, const eegspec_xform_params *p,
+                                            int nperseg, int noverlap, int64_t out_cols);
+int eegspec_eeg_transform_stft_f32(const float *x, int64_t batch, int64_t length, int32_t n_ch,
+                                   int64_t rec_stride, const eegspec_xform_params *p, int nperseg,
+                                   int noverlap, int64_t out_cols, float eps, float *out,
+                                   void *workspace, size_t workspace_bytes, void *stream);
 
 /* Number of kernel launches issued by this library since load (bench bookkeeping). */
 int64_t eegspec_launch_count(void);

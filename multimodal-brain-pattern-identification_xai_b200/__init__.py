@@ -32,6 +32,7 @@ _API = {
     "launch_count": "transform",
     "EEGTransformer": "eegtransformer",
     "xform_params": "eegtransformer",
+    "eeg_transform_stft": "eegtransformer",
     "shard_bounds": "sharding",
     "shard_slice": "sharding",
     "gather_spectrograms": "sharding",

@@ -81,6 +81,11 @@ SIGNATURES = {
     "eegspec_xform_out_length": (C.c_int64, [C.c_int64, C.POINTER(XformParams)]),
     "eegspec_eeg_transform_f32": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, C.c_int32, C.c_int64,
                                             C.POINTER(XformParams), C.c_void_p, C.c_void_p]),
+    "eegspec_eeg_transform_stft_workspace": (C.c_size_t, [C.c_int64, C.c_int64, C.POINTER(XformParams), C.c_int,
+                                                          C.c_int, C.c_int64]),
+    "eegspec_eeg_transform_stft_f32": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, C.c_int32, C.c_int64,
+                                                 C.POINTER(XformParams), C.c_int, C.c_int, C.c_int64, C.c_float,
+                                                 C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
     "eegspec_launch_count": (C.c_int64, []),
 }
 

@@ -313,6 +313,55 @@ int eegspec_eeg_transform_f32(const float* x, int64_t batch, int64_t length, int
   return eegspec::eeg_transform_launch(x, batch, length, n_ch, rec_stride, p, out, static_cast<cudaStream_t>(stream));
 }
 
+// Records per pass of the transform -> STFT pipeline.  Passes small enough for the transformed rows to stay
+// in L2 (24 MB, ~150 records) were measured SLOWER than large ones: 1.20 ms against 1.05 ms per 1 024
+// records -- sixteen short launches lose more to ramp-up and tails than the 6 % of HBM traffic the
+// intermediate costs (2 x 152 KB of 5.8 MB per record).  So a pass is as large as a 320 MB workspace allows.
+static int64_t xf_stft_chunk(int64_t batch, int64_t l_out, const eegspec_xform_params* p) {
+  const int64_t per_rec = (int64_t)p->n_out * l_out * (int64_t)sizeof(float);
+  int64_t chunk = (320LL << 20) / (per_rec > 0 ? per_rec : 1);
+  if (chunk < 1) chunk = 1;
+  return chunk < batch ? chunk : batch;
+}
+
+size_t eegspec_eeg_transform_stft_workspace(int64_t batch, int64_t length, const eegspec_xform_params* p, int nperseg,
+                                            int noverlap, int64_t out_cols) {
+  if (!p || batch <= 0 || length <= 0) return 0;
+  const int64_t l_out = eegspec::xform_out_length(length, p);
+  const int64_t chunk = xf_stft_chunk(batch, l_out, p);
+  const size_t mid = ((size_t)chunk * p->n_out * l_out * sizeof(float) + 255) & ~(size_t)255;
+  return mid + stft_image_workspace(chunk * p->n_out, l_out, nperseg, noverlap, out_cols);
+}
+
+int eegspec_eeg_transform_stft_f32(const float* x, int64_t batch, int64_t length, int32_t n_ch, int64_t rec_stride,
+                                   const eegspec_xform_params* p, int nperseg, int noverlap, int64_t out_cols,
+                                   float eps, float* out, void* workspace, size_t workspace_bytes, void* stream) {
+  if (!x || !out || !p || batch <= 0 || length <= 0) return EEGSPEC_EINVAL;
+  const size_t need = eegspec_eeg_transform_stft_workspace(batch, length, p, nperseg, noverlap, out_cols);
+  if (!workspace || workspace_bytes < need) return EEGSPEC_EWORKSPACE;
+  if (reinterpret_cast<uintptr_t>(workspace) & 15) return EEGSPEC_EALIGN;
+  eegspec_stft_plan pl;
+  const int64_t l_out = eegspec::xform_out_length(length, p);
+  int rc = stft_plan_make(l_out, nperseg, noverlap, out_cols, &pl);
+  if (rc != EEGSPEC_OK) return rc;
+  eegspec_xform_params q = *p;
+  q.out_channel_major = 1;   // rows of L_out samples: the layout the STFT kernel reads
+  const int64_t chunk = xf_stft_chunk(batch, l_out, p);
+  const size_t mid_bytes = ((size_t)chunk * p->n_out * l_out * sizeof(float) + 255) & ~(size_t)255;
+  float* mid = static_cast<float*>(workspace);
+  void* ws2 = static_cast<char*>(workspace) + mid_bytes;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  for (int64_t r0 = 0; r0 < batch; r0 += chunk) {
+    const int64_t nb = batch - r0 < chunk ? batch - r0 : chunk;
+    rc = eeg_transform_launch(x + r0 * rec_stride, nb, length, n_ch, rec_stride, &q, mid, st);
+    if (rc != EEGSPEC_OK) return rc;
+    rc = stft_image_launch(mid, nb * p->n_out, l_out, l_out, nperseg, noverlap, out_cols, eps,
+                           out + r0 * (int64_t)p->n_out * pl.n_freqs * out_cols, ws2, workspace_bytes - mid_bytes, st);
+    if (rc != EEGSPEC_OK) return rc;
+  }
+  return EEGSPEC_OK;
+}
+
 int64_t eegspec_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 
 }  // extern "C"

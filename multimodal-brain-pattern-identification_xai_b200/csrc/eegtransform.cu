@@ -177,9 +177,9 @@ __global__ void __launch_bounds__(kXfThreads) eeg_transform_kernel(const XfArgs 
   }
 }
 
-// ----------------------------------------------------------------- span kernel (downsample 5)
+// ----------------------------------------------------------------- span kernels (downsample 5)
 // The default configuration (clip / NaN / scale, Butterworth, downsample 5) when the filter
-// forgets quickly: the host takes this kernel only if the state transition over three chunks
+// forgets quickly: the host takes the lane kernel below only if the state transition over three chunks
 // (120 samples) is below 1e-9 (1.9e-11 for the reference's filter, far under fp32 resolution);
 // slower filters keep the exact block scan above.  Differences from that kernel:
 //   * the state at the start of a chunk is rebuilt from the zero-state ends of the THREE chunks
@@ -189,13 +189,12 @@ __global__ void __launch_bounds__(kXfThreads) eeg_transform_kernel(const XfArgs 
 //     than the first starts three chunks early and discards those outputs.  The cut changes no bit
 //     of the result (the warm-up chunks provide exactly the z the formula wants); the host picks
 //     the number of spans that fills whole waves of resident CTAs;
-//   * tiles of 10 chunks x 40 samples arrive by bulk copy (TMA) into a double buffer, the copy of
+//   * tiles of chunks x 40 samples arrive by bulk copy (TMA) into a double buffer, the copy of
 //     tile i + 1 runs under the arithmetic of tile i (the kernel above waits for every tile);
-//   * thread = (chunk, output channel) packed flat: 10 x 19 = 190 of 192 lanes work (19 of 32
-//     before); chunk rows are padded so that the chunks a warp spans start 20 banks apart;
 //   * the recurrence keeps two FMAs on its critical path (the b_i x + z_{i+1} halves do not depend
 //     on y); the scale is folded into b.
-// Measured (1 024 records of (10000, 20) -> (2000, 19)): 0.21 ms = 4.6 TB/s, 0.36 ms before.
+// (A first version with thread = (chunk, channel) packed flat and a shared-memory state ring reached
+// 0.21 ms per 1 024 records; git history keeps it.)
 constexpr int kSpP = 8;                      // decimated outputs per chunk
 constexpr int kSpDs = 5;
 constexpr int kSpChunk = kSpP * kSpDs;       // 40 samples
@@ -216,160 +215,8 @@ struct SpArgs {
   int sel_a[EEGSPEC_MAX_XF_CH], sel_b[EEGSPEC_MAX_XF_CH];
 };
 
-template <int NC, bool DIFF>
-__global__ void __launch_bounds__(32 * kSpChunks) eeg_transform_span_kernel(const SpArgs a) {
-  extern __shared__ __align__(128) float xs[];   // [2][kSpChunks][stride] tiles, then [3][kSpChunks][4][nz] chunk states
-  __shared__ __align__(8) uint64_t full[2];
-
-  const int tid = threadIdx.x;
-  const int k = tid / a.n_out, c = tid - k * a.n_out;
-  const bool live = k < kSpChunks;
-  const int ca = live ? a.sel_a[c] : 0, cb = (DIFF && live) ? a.sel_b[c] : 0;
-  const long long rec = blockIdx.x / a.units;
-  const int unit = blockIdx.x - (int)rec * a.units;
-  const float* xr = a.x + rec * a.rec_stride;
-  const long long span_start = (long long)unit * a.span;
-  const long long span_end = min(a.length, span_start + a.span);
-  const long long t_begin = span_start - (unit ? kSpWarm * kSpChunk : 0);
-  const int n_tiles = (int)((span_end - t_begin + kSpTile - 1) / kSpTile);
-  const uint32_t xs_u32 = c_smem_u32(xs), bar0 = c_smem_u32(&full[0]);
-  const int buf_floats = kSpChunks * a.stride;
-  const int nz = (a.n_out + 3) & ~3, zs_ring = kSpChunks * EEGSPEC_XF_ORDER * nz;
-  float* zs = xs + 2 * buf_floats;
-
-  if (tid == 0) {
-    c_mbar_init(bar0, 1);
-    c_mbar_init(bar0 + 8, 1);
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-  }
-  for (int i = tid; i < 3 * zs_ring; i += blockDim.x) zs[i] = 0.f;   // "the tile before the first": zero state
-  __syncthreads();
-
-  auto issue = [&](int tile) {   // one thread: the valid rows of each chunk, one bulk copy per chunk
-    const long long t0 = t_begin + (long long)tile * kSpTile;
-    const uint32_t bar = bar0 + 8u * (tile & 1);
-    const uint32_t dst = xs_u32 + 4u * (uint32_t)((tile & 1) * buf_floats);
-    int rows_total = (int)min((long long)kSpTile, span_end - t0);
-    c_mbar_expect_tx(bar, (uint32_t)rows_total * NC * 4u);
-    for (int kk = 0; kk < kSpChunks && rows_total > 0; ++kk, rows_total -= kSpChunk) {
-      const int rows = min(rows_total, kSpChunk);
-      c_bulk_g2s(dst + 4u * (uint32_t)(kk * a.stride), xr + (t0 + (long long)kk * kSpChunk) * NC,
-                 (uint32_t)rows * NC * 4u, bar);
-    }
-  };
-  if (tid == 0) issue(0);
-
-  const float b0 = a.b[0], b1 = a.b[1], b2 = a.b[2], b3 = a.b[3], b4 = a.b[4];
-  const float na1 = -a.a[1], na2 = -a.a[2], na3 = -a.a[3], na4 = -a.a[4];
-  const float clip = a.clip;
-  const long long o_begin = span_start / kSpDs, o_end = (span_end + kSpDs - 1) / kSpDs;
-
-  for (int tile = 0; tile < n_tiles; ++tile) {
-    if (tid == 0 && tile + 1 < n_tiles) issue(tile + 1);   // its buffer was last read two barriers ago
-    c_mbar_wait(bar0 + 8u * (tile & 1), (tile >> 1) & 1);
-    const long long t_chunk = t_begin + (long long)tile * kSpTile + (long long)k * kSpChunk;
-    const int rows = live ? (int)max(0LL, min((long long)kSpChunk, span_end - t_chunk)) : 0;
-    const float* xp = xs + (tile & 1) * buf_floats + (live ? k : 0) * a.stride;
-
-    float yz[kSpP];
-    float z0 = 0.f, z1 = 0.f, z2 = 0.f, z3 = 0.f;
-#define XF_STEP(n, keep)                                                   \
-  {                                                                        \
-    float v = xp[(n) * NC + ca];                                           \
-    if (DIFF) v -= xp[(n) * NC + cb];                                      \
-    v = (v != v) ? 0.f : fminf(fmaxf(v, -clip), clip);                     \
-    const float t0 = fmaf(b1, v, z1), t1 = fmaf(b2, v, z2), t2 = fmaf(b3, v, z3), t3 = b4 * v; \
-    const float y = fmaf(b0, v, z0);                                       \
-    z0 = fmaf(na1, y, t0);                                                 \
-    z1 = fmaf(na2, y, t1);                                                 \
-    z2 = fmaf(na3, y, t2);                                                 \
-    z3 = fmaf(na4, y, t3);                                                 \
-    if (keep) yz[(n) / kSpDs] = y;                                         \
-  }
-    if (rows == kSpChunk) {
-#pragma unroll
-      for (int n = 0; n < kSpChunk; ++n) XF_STEP(n, (n % kSpDs) == 0)
-    } else {   // the record (or the span) ends inside this chunk: later chunks are never stored
-#pragma unroll
-      for (int m = 0; m < kSpP; ++m) {
-        yz[m] = 0.f;
-        for (int r = 0; r < kSpDs; ++r) {
-          const int n = m * kSpDs + r;
-          if (n < rows) {
-            float v = xp[n * NC + ca];
-            if (DIFF) v -= xp[n * NC + cb];
-            v = (v != v) ? 0.f : fminf(fmaxf(v, -clip), clip);
-            const float t0 = fmaf(b1, v, z1), t1 = fmaf(b2, v, z2), t2 = fmaf(b3, v, z3), t3 = b4 * v;
-            const float y = fmaf(b0, v, z0);
-            z0 = fmaf(na1, y, t0);
-            z1 = fmaf(na2, y, t1);
-            z2 = fmaf(na3, y, t2);
-            z3 = fmaf(na4, y, t3);
-            if (r == 0) yz[m] = y;
-          }
-        }
-      }
-    }
-#undef XF_STEP
-    float* zt = zs + (tile % 3) * zs_ring;                 // this tile's ring slot
-    const float* zp = zs + ((tile + 2) % 3) * zs_ring;     // the previous tile's
-    if (live) {
-      float* z = zt + k * EEGSPEC_XF_ORDER * nz + c;
-      z[0] = z0; z[nz] = z1; z[2 * nz] = z2; z[3 * nz] = z3;
-    }
-    __syncthreads();
-    // ---- state at the start of chunk k = z_{k-1} + M z_{k-2} + M^2 z_{k-3}: the zero-state ends of the three
-    // chunks before it; what older chunks left is below 1e-9 of them (the host checked M^3) and is dropped.
-    // Ring of three slots: a slot is rewritten two barriers after its last reader.
-    if (live) {
-      const float* q1 = (k >= 1 ? zt + (k - 1) * EEGSPEC_XF_ORDER * nz : zp + (k + 9) * EEGSPEC_XF_ORDER * nz) + c;
-      const float* q2 = (k >= 2 ? zt + (k - 2) * EEGSPEC_XF_ORDER * nz : zp + (k + 8) * EEGSPEC_XF_ORDER * nz) + c;
-      const float* q3 = (k >= 3 ? zt + (k - 3) * EEGSPEC_XF_ORDER * nz : zp + (k + 7) * EEGSPEC_XF_ORDER * nz) + c;
-      const float u0 = q2[0], u1 = q2[nz], u2 = q2[2 * nz], u3 = q2[3 * nz];
-      const float w0 = q3[0], w1 = q3[nz], w2 = q3[2 * nz], w3 = q3[3 * nz];
-      float f[EEGSPEC_XF_ORDER];
-#pragma unroll
-      for (int i = 0; i < EEGSPEC_XF_ORDER; ++i)
-        f[i] = q1[i * nz] + (a.m[i][0] * u0 + a.m[i][1] * u1 + a.m[i][2] * u2 + a.m[i][3] * u3) +
-               (a.m2[i][0] * w0 + a.m2[i][1] * w1 + a.m2[i][2] * w2 + a.m2[i][3] * w3);
-#pragma unroll
-      for (int m = 0; m < kSpP; ++m)
-        yz[m] += a.g[0][m] * f[0] + a.g[1][m] * f[1] + a.g[2][m] * f[2] + a.g[3][m] * f[3];
-    }
-    if (a.mu_law) {
-#pragma unroll
-      for (int m = 0; m < kSpP; ++m) yz[m] = xf_mu_law(yz[m], a.mu, a.mu_scale);
-    }
-    if (live) {
-      const long long o0 = t_chunk / kSpDs;
-      const bool whole = o0 >= o_begin && o0 + kSpP <= o_end;
-      if (a.out_channel_major) {
-        float* o = a.out + (rec * a.n_out + c) * a.l_out + o0;
-        if (whole && !((a.l_out | reinterpret_cast<uintptr_t>(a.out) >> 2) & 3)) {   // one full sector per thread
-          reinterpret_cast<float4*>(o)[0] = make_float4(yz[0], yz[1], yz[2], yz[3]);
-          reinterpret_cast<float4*>(o)[1] = make_float4(yz[4], yz[5], yz[6], yz[7]);
-        } else {
-#pragma unroll
-          for (int m = 0; m < kSpP; ++m)
-            if (whole || (o0 + m >= o_begin && o0 + m < o_end)) o[m] = yz[m];
-        }
-      } else if (whole && a.n_out == 19) {   // constant offsets
-        float* o = a.out + (rec * a.l_out + o0) * 19 + c;
-#pragma unroll
-        for (int m = 0; m < kSpP; ++m) o[m * 19] = yz[m];
-      } else {
-        float* o = a.out + (rec * a.l_out + o0) * a.n_out + c;
-#pragma unroll
-        for (int m = 0; m < kSpP; ++m)
-          if (whole || (o0 + m >= o_begin && o0 + m < o_end)) o[(long long)m * a.n_out] = yz[m];
-      }
-    }
-  }
-}
-
 // ------------------------------------------------------- span kernel, one warp per 4 channels
-// Same arithmetic and the same cut into spans as the kernel above; the difference is who talks to
-// whom.  A warp owns FOUR output channels for the whole span: lane = (chunk k' of the tile's 8,
+// A warp owns FOUR output channels for the whole span: lane = (chunk k' of the tile's 8,
 // channel cc of the warp's 4).  The three previous chunks a lane needs live in the SAME warp (the
 // lanes 4, 8 and 12 below it, or the warp's own registers of the previous tile), so the chunk
 // states travel by shuffle: no shared-memory state ring and no CTA barrier in the loop.  Warps
@@ -628,23 +475,13 @@ static int span_launch(const float* x, long long batch, long long length, int n_
     for (int r = 0; r < EEGSPEC_XF_ORDER; ++r) decay = fmax(decay, fabs(z[r]));
   }
   if (!(decay < 1e-9)) return kSpanNotApplicable;   // a slowly decaying filter: the exact block scan above
-  const char* which = getenv("EEGSPEC_XF_KERNEL");
-  const bool lanes = !(which && !strcmp(which, "span")) && length < (1LL << 30);   // default: one warp per 4 channels
-  size_t smem;
-  int threads;
-  void (*kernel)(const SpArgs);
-  if (lanes) {
-    a.stride = kSpChunk * n_ch + 4;
-    smem = sizeof(float) * 2 * (size_t)kLnChunks * a.stride;
-    threads = 32 * ((p->n_out + 3) / 4);
-    kernel = diff ? eeg_transform_lane_kernel<8, true> : eeg_transform_lane_kernel<20, false>;
-  } else {
-    a.stride = kSpChunk * n_ch + ((p->n_out + 3) & ~3);
-    smem = sizeof(float) * (2 * (size_t)kSpChunks * a.stride +
-                            3 * (size_t)kSpChunks * EEGSPEC_XF_ORDER * ((p->n_out + 3) & ~3));
-    threads = (kSpChunks * p->n_out + 31) & ~31;
-    kernel = diff ? eeg_transform_span_kernel<8, true> : eeg_transform_span_kernel<20, false>;
-  }
+  if (length >= (1LL << 30)) return kSpanNotApplicable;
+  a.stride = kSpChunk * n_ch + 4;   // chunk rows 4 (n_ch = 20, 8) or 28 (n_ch = 19) banks apart: conflict-free
+  const size_t smem = sizeof(float) * 2 * (size_t)kLnChunks * a.stride;
+  const int threads = 32 * ((p->n_out + 3) / 4);
+  void (*kernel)(const SpArgs) = diff ? eeg_transform_lane_kernel<8, true>
+                                 : n_ch == 19 ? eeg_transform_lane_kernel<19, false>
+                                              : eeg_transform_lane_kernel<20, false>;
   cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return (int)e;
   int dev = 0, sms = 0, occ = 0;
@@ -656,7 +493,7 @@ static int span_launch(const float* x, long long batch, long long length, int n_
   const long long n_chunks = (length + kSpChunk - 1) / kSpChunk;
   int best_units = 1;
   long long best_span = n_chunks * kSpChunk;
-  if (!getenv("EEGSPEC_XF_ONE_SPAN")) {
+  {
     double best = 0.0;
     for (int u = 1; u <= 32; ++u) {
       const long long span = (n_chunks + u - 1) / u * kSpChunk;
@@ -682,7 +519,11 @@ int eeg_transform_launch(const float* x, long long batch, long long length, int 
   if (p->n_out < 1 || p->n_out > EEGSPEC_MAX_XF_CH) return EEGSPEC_EINVAL;
   const int ds = p->downsample < 1 ? 1 : p->downsample;
   if (ds > 8) return EEGSPEC_EUNSUPPORTED;
-  if ((n_ch & 3) || (rec_stride & 3) || (reinterpret_cast<uintptr_t>(x) & 15)) return EEGSPEC_EALIGN;   // 16-byte cp.async
+  // 16-byte copies (cp.async / TMA) of whole sample rows: every record and every tile of 40 rows must start
+  // on a 16-byte boundary and hold a whole number of 16-byte words -- any n_ch when length % 4 == 0
+  // (the reference's (10000, 19) windows), n_ch % 4 == 0 otherwise.
+  if ((rec_stride & 3) || (reinterpret_cast<uintptr_t>(x) & 15)) return EEGSPEC_EALIGN;
+  if ((n_ch & 3) && (length & 3)) return EEGSPEC_EALIGN;
   for (int c = 0; c < p->n_out; ++c)
     if (p->sel_a[c] < 0 || p->sel_a[c] >= n_ch || p->sel_b[c] >= n_ch) return EEGSPEC_EINVAL;
   if (p->filter && fabs(p->a[0] - 1.0) > 1e-12) return EEGSPEC_EINVAL;
@@ -723,7 +564,7 @@ int eeg_transform_launch(const float* x, long long batch, long long length, int 
   for (int c = 0; c < p->n_out; ++c) { any_diff |= p->sel_b[c] >= 0; all_diff &= p->sel_b[c] >= 0; }
   const bool fast = ds == 5 && p->normalize && p->filter && (any_diff == all_diff);
   if (batch > 0x7fffffffLL) return EEGSPEC_EUNSUPPORTED;
-  if (fast && ((n_ch == 20 && !all_diff) || (n_ch == 8 && all_diff)) && !getenv("EEGSPEC_XF_RECORD_KERNEL")) {
+  if (fast && (((n_ch == 20 || n_ch == 19) && !all_diff) || (n_ch == 8 && all_diff))) {
     const int rc = span_launch(x, batch, length, n_ch, rec_stride, p, out, all_diff, st);
     if (rc != kSpanNotApplicable) return rc;
   }

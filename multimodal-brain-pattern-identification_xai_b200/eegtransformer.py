@@ -89,9 +89,9 @@ class EEGTransformer:
         need = max(max(self.params.sel_a[i], self.params.sel_b[i]) for i in range(self.params.n_out)) + 1
         if n_ch < need:
             raise ValueError(f"{n_ch} channels given, the selection needs {need}")
-        if n_ch % 4:                                        # float4 tile loads: pad the channel axis
-            t = torch.nn.functional.pad(t, (0, 4 - n_ch % 4))
-            n_ch = t.shape[2]
+        if n_ch % 4 and length % 4:     # 16-byte row copies need whole words per record: the reference's
+            t = torch.nn.functional.pad(t, (0, 4 - n_ch % 4))   # (10000, 19) windows go in as they are,
+            n_ch = t.shape[2]                                   # only odd lengths of odd widths are padded
         t = t.contiguous()
         l_out = int(nat.lib.eegspec_xform_out_length(length, C.byref(self.params)))
         shape = (batch, self.params.n_out, l_out) if self.params.out_channel_major else (batch, l_out, self.params.n_out)
@@ -105,3 +105,39 @@ class EEGTransformer:
         if as_numpy:
             return out.cpu().numpy()
         return out.to(src_device)
+
+
+def eeg_transform_stft(x: torch.Tensor, config, transformer: Optional[EEGTransformer] = None) -> torch.Tensor:
+    """Raw EEG windows -> the DiffEEG spectrogram condition in one call.
+
+    ``x``: (B, L, C) time-major raw EEG on the device (the (10000, 19) windows of ``_get_eeg_window``).
+    Equivalent to ``compute_stft(transformer.transform(x, channel_major), config)`` -- the reference's
+    ``EEGDataset`` transform (dataset.py:73-104, :213-228) followed by ``compute_stft``
+    (DiffEEG_utils.py:27-76, called at DiffEEG_train.py:131): one C-ABI call, two launches per pass of
+    ~2 000 records, the transformed (C, L/5) rows (3 % of the image bytes) in a workspace between them.
+    Returns (B, n_out, F, 2000)."""
+    from .transform import EPS, OUT_COLS, _stft_keys
+
+    _require_cuda()
+    tr = transformer if transformer is not None else EEGTransformer(n_feats=19, downsample=5)
+    nperseg, noverlap = _stft_keys(config)
+    if x.dim() != 3 or not x.is_cuda:
+        raise ValueError("eeg_transform_stft expects a (B, L, C) tensor on the device")
+    t = x.to(dtype=torch.float32).contiguous()
+    batch, length, n_ch = t.shape
+    if n_ch % 4 and length % 4:
+        t = torch.nn.functional.pad(t, (0, 4 - n_ch % 4)).contiguous()
+        n_ch = t.shape[2]
+    p = tr.params
+    n_freqs = nperseg // 2 + 1
+    out = torch.empty((batch, p.n_out, n_freqs, OUT_COLS), device=t.device, dtype=torch.float32)
+    if batch == 0:
+        return out
+    with torch.cuda.device(t.device):
+        ws_bytes = nat.lib.eegspec_eeg_transform_stft_workspace(batch, length, C.byref(p), nperseg, noverlap, OUT_COLS)
+        ws = torch.empty(ws_bytes, dtype=torch.uint8, device=t.device)
+        nat.check(nat.lib.eegspec_eeg_transform_stft_f32(_ptr(t), batch, length, n_ch, length * n_ch, C.byref(p),
+                                                         nperseg, noverlap, OUT_COLS, EPS, _ptr(out), _ptr(ws),
+                                                         ws_bytes, _stream_ptr(t.device)),
+                  "eeg_transform_stft")
+    return out

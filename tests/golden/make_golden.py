@@ -132,6 +132,10 @@ XFORM_CASES = {
     # appended later: the draws above are unchanged
     "mu_law": (10000, 20, dict(n_feats=19, apply_mu_law_encoding=True, downsample=5), "eeg"),
     "mu_law_nofilter_nan": (3000, 20, dict(n_feats=19, apply_butter_lowpass_filter=False, apply_mu_law_encoding=True, downsample=2), "nan"),
+    # the reference's real input: the (10000, 19) window of _get_eeg_window (cfg_utils.py:366-373), no EKG column
+    "window19": (10000, 19, dict(n_feats=19, downsample=5), "nan"),
+    "window19_ds4": (3000, 19, dict(n_feats=19, downsample=4), "eeg"),
+    "window19_odd_length": (2001, 19, dict(n_feats=19, downsample=5), "eeg"),
 }
 
 

@@ -62,6 +62,26 @@ def test_feeds_compute_stft():
     assert np.abs(img.cpu().numpy() - want).max() <= 1e-3
 
 
+def test_fused_transform_stft_equals_the_two_calls():
+    """eeg_transform_stft (one C-ABI call) == transform + compute_stft, bit for
+    bit, and both match the two lifted reference pieces chained (oracle ports) within 1e-3."""
+    rng = np.random.default_rng(35)
+    x = (np.cumsum(rng.standard_normal((300, 10000, 19)), 1) + rng.standard_normal((300, 10000, 19)) * 30).astype(np.float32)
+
+    class Cfg:
+        diffEEG_trainer = {"stft_n_fft": 64, "stft_hop_length": 32, "stft_window": "hann"}
+
+    xt = torch.from_numpy(x).cuda()
+    tr = b200spec.EEGTransformer(n_feats=19, downsample=5, channel_major=True)
+    fused = b200spec.eeg_transform_stft(xt, Cfg)
+    two = b200spec.compute_stft(tr.transform(xt), Cfg)
+    assert fused.shape == (300, 19, 33, 2000) and torch.equal(fused, two)
+    from oracle import stft_oracle
+    ref_sig = np.transpose(eo.eeg_transform_batch_oracle(x[:2], n_feats=19, downsample=5), (0, 2, 1)).astype(np.float32)
+    want = stft_oracle.compute_stft_port(ref_sig, Cfg)
+    assert np.abs(fused[:2].cpu().numpy() - want).max() <= 1e-3
+
+
 def test_errors():
     with pytest.raises(ValueError):
         b200spec.EEGTransformer(n_feats=19).transform(torch.zeros(100, 10, device="cuda"))      # too few channels
@@ -71,34 +91,48 @@ def test_errors():
         b200spec.EEGTransformer(n_feats=19, downsample=16).transform(torch.zeros(1000, 20, device="cuda"))
 
 
-def test_span_cuts_do_not_change_a_bit(monkeypatch):
-    """The default configuration runs the span kernel, which cuts a record into spans to fill whole
-    waves (the cut depends on the batch size).  The state at a chunk start is rebuilt from the
-    zero-state ends of the three chunks before it, warm-up chunks included, so a cut record equals
-    an uncut one bit for bit; the per-record block-scan kernel (exact carry) agrees to rounding."""
+def test_span_cuts_do_not_change_a_bit():
+    """The default configuration runs the lane kernel, which cuts a record into spans to fill whole
+    waves: the cut depends on the batch size.  The state at a chunk start is rebuilt from the
+    zero-state ends of the three chunks before it, warm-up chunks included, so a record transformed
+    alone (many spans), in a batch of 5 or in a batch of 300 (one span) is the same bit for bit --
+    for the (L, 20) parquet rows and for the reference's (L, 19) windows."""
     rng = np.random.default_rng(33)
     x = (np.cumsum(rng.standard_normal((5, 10000, 20)), 1) + rng.standard_normal((5, 10000, 20)) * 30).astype(np.float32)
     x[1, 4000:4100, 3] = np.nan
     x[2, :, 7] = 5000.0                                   # clipped to 1024
-    xt = torch.from_numpy(x).cuda()
-    for kw in (dict(n_feats=19, downsample=5), dict(n_feats=19, downsample=5, channel_major=True)):
-        t = b200spec.EEGTransformer(**kw)
-        cut = t.transform(xt)
-        monkeypatch.setenv("EEGSPEC_XF_ONE_SPAN", "1")
-        assert torch.equal(cut, t.transform(xt))
-        monkeypatch.delenv("EEGSPEC_XF_ONE_SPAN")
-        monkeypatch.setenv("EEGSPEC_XF_KERNEL", "span")     # the shared-memory state ring variant: same arithmetic
-        assert torch.equal(cut, t.transform(xt))
-        monkeypatch.delenv("EEGSPEC_XF_KERNEL")
-        monkeypatch.setenv("EEGSPEC_XF_RECORD_KERNEL", "1")
-        scan = t.transform(xt)
-        monkeypatch.delenv("EEGSPEC_XF_RECORD_KERNEL")
-        assert (cut - scan).abs().max().item() <= 1e-4   # fp32 recurrences in a different order, values up to 32
+    for cols in (20, 19):
+        xt = torch.from_numpy(np.ascontiguousarray(x[:, :, :cols])).cuda()
+        big = xt.repeat(60, 1, 1)
+        for kw in (dict(n_feats=19, downsample=5), dict(n_feats=19, downsample=5, channel_major=True)):
+            t = b200spec.EEGTransformer(**kw)
+            cut = t.transform(xt)
+            for r in range(5):
+                assert torch.equal(cut[r], t.transform(xt[r]))
+            assert torch.equal(t.transform(big)[295:300], cut)
+            want = eo.eeg_transform_batch_oracle(x[:, :, :cols], n_feats=19, downsample=5)
+            got = cut.transpose(1, 2) if kw.get("channel_major") else cut
+            assert np.abs(got.cpu().numpy() - want).max() <= ATOL
     x8 = np.ascontiguousarray(x[:, :, :8])
     t8 = b200spec.EEGTransformer(n_feats=8, apply_chris_magic_ch8=True, downsample=5)
     got = t8.transform(x8)
     want = eo.eeg_transform_batch_oracle(x8, n_feats=8, apply_chris_magic_ch8=True, downsample=5)
     assert np.abs(got - want).max() <= ATOL
+
+
+def test_window19_runs_without_a_padding_copy():
+    """(B, 10000, 19) goes straight into the kernel: one launch, no torch kernel in front of it."""
+    x = torch.randn(8, 10000, 19, device="cuda") * 40
+    t = b200spec.EEGTransformer(n_feats=19, downsample=5)
+    t.transform(x)
+    torch.cuda.synchronize()
+    before = b200spec.launch_count()
+    with torch.profiler.profile(activities=[torch.profiler.ProfilerActivity.CUDA]) as prof:
+        y = t.transform(x)
+        torch.cuda.synchronize()
+    assert b200spec.launch_count() - before == 1 and y.shape == (8, 2000, 19)
+    kernels = [e.key for e in prof.key_averages() if e.device_type == torch.autograd.DeviceType.CUDA]
+    assert all("eeg_transform" in k for k in kernels), kernels
 
 
 @pytest.mark.parametrize("length", [40, 1234, 9999, 10003])

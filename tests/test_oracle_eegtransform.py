@@ -18,6 +18,10 @@ CASES = {
     "raw_scale": dict(n_feats=19, normalize=False, downsample=3),
     "mu_law": dict(n_feats=19, apply_mu_law_encoding=True, downsample=5),
     "mu_law_nofilter_nan": dict(n_feats=19, apply_butter_lowpass_filter=False, apply_mu_law_encoding=True, downsample=2),
+    # (L, 19): the window _get_eeg_window hands the transformer (cfg_utils.py:366-373) -- no EKG column
+    "window19": dict(n_feats=19, downsample=5),
+    "window19_ds4": dict(n_feats=19, downsample=4),
+    "window19_odd_length": dict(n_feats=19, downsample=5),
 }
 
 
