@@ -221,6 +221,30 @@ int eegspec_eeg_transform_stft_f32(const float *x, int64_t batch, int64_t length
                                    int noverlap, int64_t out_cols, float eps, float *out,
                                    void *workspace, size_t workspace_bytes, void *stream);
 
+/* ------------------------------------------------------------------------------------------
+ * Row (f)2 -- the consumer of the path: spectrogram-condition front end of the DiffEEG denoiser
+ *   replaces /root/reference/root/src/models/diffEEG.py:47-53 (ConvTranspose2d(C -> H2, kernel (3, 3),
+ *   stride (1, 8), padding (1, 2))), :108-110 (relu -> flatten(start_dim=2) -> F.interpolate(size=T,
+ *   mode="linear", align_corners=False)) and :136-145 (within-class mixing, training mode) with the
+ *   random permutation made explicit: partner[b] is the record b is mixed with.
+ * The 527 703-sample intermediate per output channel is never formed: each output sample gathers the
+ * two convolution outputs the interpolation keeps.
+ * ------------------------------------------------------------------------------------------ */
+typedef struct eegspec_cond_params {
+  int32_t n_channels;    /* C: input channels of the image (19 or 8)                      */
+  int32_t n_freqs;       /* F: 33                                                         */
+  int32_t n_cols;        /* image columns, 2000                                           */
+  int32_t out_channels;  /* H2 = hidden_channels / 2 (16 in the shipped config)           */
+  int32_t out_length;    /* T = x.shape[-1] of the denoiser input, 2000                   */
+  float mix_alpha;       /* 0.5 (diffEEG.py:142); only read when partner != NULL          */
+} eegspec_cond_params;
+
+/* spec: device (batch, C, F, n_cols) fp32; weight: device (C, H2, 3, 3), the ConvTranspose2d layout;
+ * bias: device (H2); partner: device int32 (batch) or NULL; out: device (batch, H2, T) fp32. */
+int eegspec_spec_condition_f32(const float *spec, int64_t batch, const eegspec_cond_params *p,
+                               const float *weight, const float *bias, const int32_t *partner,
+                               float *out, void *stream);
+
 /* Number of kernel launches issued by this library since load (bench bookkeeping). */
 int64_t eegspec_launch_count(void);
 

@@ -30,6 +30,7 @@ _API = {
     "melspec_geometry": "transform",
     "install": "transform",
     "launch_count": "transform",
+    "spectrogram_condition": "diffeeg",
     "EEGTransformer": "eegtransformer",
     "xform_params": "eegtransformer",
     "eeg_transform_stft": "eegtransformer",

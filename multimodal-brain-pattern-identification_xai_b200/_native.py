@@ -48,6 +48,11 @@ class XformParams(C.Structure):
     ]
 
 
+class CondParams(C.Structure):
+    _fields_ = [("n_channels", C.c_int32), ("n_freqs", C.c_int32), ("n_cols", C.c_int32),
+                ("out_channels", C.c_int32), ("out_length", C.c_int32), ("mix_alpha", C.c_float)]
+
+
 # name -> (restype, argtypes); mirrors include/eegspec.h one to one.
 SIGNATURES = {
     "eegspec_abi_version": (C.c_int, []),
@@ -86,6 +91,8 @@ SIGNATURES = {
     "eegspec_eeg_transform_stft_f32": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, C.c_int32, C.c_int64,
                                                  C.POINTER(XformParams), C.c_int, C.c_int, C.c_int64, C.c_float,
                                                  C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
+    "eegspec_spec_condition_f32": (C.c_int, [C.c_void_p, C.c_int64, C.POINTER(CondParams), C.c_void_p, C.c_void_p,
+                                             C.c_void_p, C.c_void_p, C.c_void_p]),
     "eegspec_launch_count": (C.c_int64, []),
 }
 

@@ -362,6 +362,11 @@ int eegspec_eeg_transform_stft_f32(const float* x, int64_t batch, int64_t length
   return EEGSPEC_OK;
 }
 
+int eegspec_spec_condition_f32(const float* spec, int64_t batch, const eegspec_cond_params* p, const float* weight,
+                               const float* bias, const int32_t* partner, float* out, void* stream) {
+  return spec_condition_launch(spec, batch, p, weight, bias, partner, out, static_cast<cudaStream_t>(stream));
+}
+
 int64_t eegspec_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 
 }  // extern "C"

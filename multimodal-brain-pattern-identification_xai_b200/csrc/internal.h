@@ -40,6 +40,10 @@ int melspec_sliding_launch(const float* eeg, int n_ch, long long total_length, l
                            const eegspec_mel_params* p, float* out, void* workspace, size_t workspace_bytes,
                            cudaStream_t st);
 
+// spec_condition.cu
+int spec_condition_launch(const float* spec, long long batch, const eegspec_cond_params* p, const float* weight,
+                          const float* bias, const int* partner, float* out, cudaStream_t st);
+
 // eegtransform.cu
 void xform_params_default(eegspec_xform_params* p);
 long long xform_out_length(long long length, const eegspec_xform_params* p);

@@ -173,3 +173,26 @@ def load_reference_data_utils(names, feature_names=None):
     except Exception:   # skimage is not in this image; only resample_spectrogram needs it
         pass
     return lift_functions(_DATA_UTILS, names, env)
+
+
+# --------------------------------------------------------------------------- DiffEEG (row f2)
+_DIFFEEG_MODEL = os.path.join(REFERENCE_ROOT, "root", "src", "models", "diffEEG.py")
+
+
+def load_reference_diffeeg(n_channels: int = 19, hidden_channels: int = 32, n_classes: int = 6, dropout: float = 0.1):
+    """The reference ``DiffEEG`` module (/root/reference/root/src/models/diffEEG.py:20-145) on CPU, lifted with
+    its ``GTU`` helper; ``config`` is a stub with the keys its constructor reads (:23-31)."""
+    import random
+
+    import numpy as np
+    import torch
+    import torch.nn as nn
+    import torch.nn.functional as F
+    import torch.utils.checkpoint as checkpoint
+
+    env = {"torch": torch, "nn": nn, "F": F, "np": np, "random": random, "checkpoint": checkpoint}
+    lift_functions(_DIFFEEG_MODEL, ["GTU", "DiffEEG"], env)
+    cfg = SimpleNamespace(device=torch.device("cpu"),
+                          diffEEG_trainer={"n_classes": n_classes, "n_channels": n_channels,
+                                           "hidden_channels": hidden_channels, "dropout": dropout})
+    return env["DiffEEG"](cfg)

@@ -261,10 +261,72 @@ def make_melspec_xcheck():
     print("wrote", path, os.path.getsize(path), "bytes")
 
 
+def diffeeg_inputs(case: str):
+    """Deterministic inputs of the row-(f)2 cases (regenerated by the tests: the images are too big to commit)."""
+    cfg = {"ship19": (3, 19, 32, 7), "ckpt8": (2, 8, 128, 8), "train19": (6, 19, 32, 9)}[case]
+    b, c, hidden, seed = cfg
+    rng = np.random.default_rng(seed)
+    spec = rng.random((b, c, 33, 2000), dtype=np.float32)          # compute_stft images live in [0, 1]
+    spec[0, 0] = 0.0                                               # a flat channel
+    return spec, c, hidden, seed
+
+
+def make_diffeeg():
+    """``diffeeg_golden.npz``: the spectrogram condition the REFERENCE's own ``DiffEEG`` computes
+    (/root/reference/root/src/models/diffEEG.py:47-53, 108-110, 136-145), lifted by ``oracle/ref_extract.py``:
+    ``<case>/hooked`` = the input of ``channel_expand`` during the reference's ``forward`` (bf16 autocast on CPU),
+    ``<case>/fp32`` = its own ``spectrogram_upsample1`` layer in fp32 + the three forward lines."""
+    import torch
+    import torch.nn.functional as F
+
+    out = {}
+    for case in ("ship19", "ckpt8", "train19"):
+        spec_np, c, hidden, seed = diffeeg_inputs(case)
+        torch.manual_seed(seed)
+        m = rx.load_reference_diffeeg(n_channels=c, hidden_channels=hidden)
+        spec = torch.from_numpy(spec_np)
+        b = spec.shape[0]
+        w, bias = m.spectrogram_upsample1.weight.detach(), m.spectrogram_upsample1.bias.detach()
+        out[f"{case}/weight"], out[f"{case}/bias"] = w.numpy(), bias.numpy()
+        labels = torch.tensor([0, 1, 0, 0, 1, 2][:b])
+        onehot = F.one_hot(labels, 6).float()
+        cap = {}
+        handle = m.channel_expand.register_forward_pre_hook(lambda mod, inp: cap.__setitem__("x", inp[0].detach().float().clone()))
+        if case == "train19":
+            m.train()
+            torch.manual_seed(1234)
+            mixed = m.recombine_spectrograms(spec, labels)          # the reference's own mixing
+            torch.manual_seed(1234)                                 # replay its randperm calls to learn the partners
+            partner = torch.arange(b)
+            for cls in range(m.n_classes):
+                idx = (labels == cls).nonzero(as_tuple=True)[0]
+                if len(idx) > 1:
+                    partner[idx] = idx[torch.randperm(len(idx))]
+            assert torch.equal(mixed, 0.5 * spec + 0.5 * spec[partner])
+            out[f"{case}/partner"] = partner.numpy().astype(np.int32)
+            spec_in = mixed
+            m.eval()
+        else:
+            spec_in = spec
+        import warnings
+        with torch.no_grad(), warnings.catch_warnings():
+            warnings.simplefilter("ignore")
+            m(torch.zeros(b, c, 2000), onehot, torch.arange(b, dtype=torch.float32) + 3, spec_in)
+            own = F.interpolate(F.relu(m.spectrogram_upsample1(spec_in)).flatten(start_dim=2), size=2000, mode="linear",
+                                align_corners=False)
+        handle.remove()
+        out[f"{case}/hooked"] = cap["x"].numpy()
+        out[f"{case}/fp32"] = own.numpy()
+    out["versions"] = np.array([f"torch {torch.__version__}", f"numpy {np.__version__}"])
+    path = os.path.join(HERE, "diffeeg_golden.npz")
+    np.savez_compressed(path, **out)
+    print("wrote", path, os.path.getsize(path), "bytes")
+
+
 if __name__ == "__main__":
     if not rx.reference_available():
         raise SystemExit("/root/reference is not mounted: golden vectors can only be made in the build container")
     only = set(sys.argv[1:])
-    for fn in (make_stft, make_melspec, make_eegtransform, make_fronthalf, make_melspec_xcheck):
+    for fn in (make_stft, make_melspec, make_eegtransform, make_fronthalf, make_melspec_xcheck, make_diffeeg):
         if not only or fn.__name__ in only:
             fn()
