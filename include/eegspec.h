@@ -245,6 +245,57 @@ int eegspec_spec_condition_f32(const float *spec, int64_t batch, const eegspec_c
                                const float *weight, const float *bias, const int32_t *partner,
                                float *out, void *stream);
 
+/* ------------------------------------------------------------------------------------------
+ * Rows (f)4 / (f)3 -- the classifier-side preprocessing of the multimodal model's two inputs
+ *   (CombinedDataset, /root/reference/root/jupyter_notebooks/XAI_Multimodality.py:1114-1307; the helpers
+ *   are the same code as /root/reference/root/src/utils/data_utils.py:129-249).
+ * ------------------------------------------------------------------------------------------ */
+#define EEGSPEC_CLS_MAX_TAPS 13
+
+/* process_eeg (:1148-1164): band-pass -> NaN fill -> 18 montage differences -> band-pass + 4-tap mean +
+ * decimate 4 -> per-row z-score -> rows 0..18 and 19..36 of the 38-row array -> pad / truncate to 3000. */
+typedef struct eegspec_cls_eeg_params {
+  int32_t n_taps1;                         /* 11: butter(5, [0.5, 20] Hz @ 200 Hz, 'band')  (:1156, :1253)        */
+  double b1[EEGSPEC_CLS_MAX_TAPS], a1[EEGSPEC_CLS_MAX_TAPS];
+  int32_t n_taps2;                         /* 13: butter(6, ...) of denoise_filter           (:1268)               */
+  double b2[EEGSPEC_CLS_MAX_TAPS], a2[EEGSPEC_CLS_MAX_TAPS];
+  int32_t n_pairs;                         /* 18 map_features pairs                           (:211-217)            */
+  int32_t pair_a[EEGSPEC_MAX_PAIRS], pair_b[EEGSPEC_MAX_PAIRS];
+  int32_t n_features;                      /* 19 = len(feature_to_index): rows kept AND the start index of the
+                                            * "differential" rows in select_and_map_channels  (:1278-1282)          */
+  int32_t fixed_length;                    /* 3000                                            (:245)                */
+  float eps;                               /* 1e-6                                            (:1276)               */
+} eegspec_cls_eeg_params;
+
+void eegspec_cls_eeg_params_default(eegspec_cls_eeg_params *p);
+size_t eegspec_classifier_eeg_workspace(int64_t batch, int64_t length, int32_t n_ch);
+
+/* x: device fp32 (batch, length, n_ch) time-major -- eeg.values of the parquet frames (n_ch = 20 EEG_COLUMNS),
+ * records `rec_stride` elements apart.  out: device (batch, 1, n_features + n_pairs, fixed_length) fp32.
+ * status: device int32 (batch) or NULL; set to 1 for a record in which a channel starts with NaN (its filtered
+ * row is all NaN: the reference drops the row and shifts every later channel -- refused, result undefined). */
+int eegspec_classifier_eeg_f32(const float *x, int64_t batch, int64_t length, int32_t n_ch, int64_t rec_stride,
+                               const eegspec_cls_eeg_params *p, float *out, int32_t *status,
+                               void *workspace, size_t workspace_bytes, void *stream);
+
+/* process_spectrogram (:1183-1202) on the (rows, cols) = (400, 300) window cut out by :1173-1183. */
+typedef struct eegspec_cls_spec_params {
+  int32_t rows, cols;                      /* 400, 300 = CFG.image_size                                           */
+  double notch_b[3], notch_a[3];           /* iirnotch(60, 30, fs=200)                        (:1294-1297)        */
+  double notch_zi[2];                      /* lfilter_zi(notch_b, notch_a): filtfilt's initial state             */
+  float gauss_sigma, gauss_truncate;       /* 1.0, 4.0 (scipy.ndimage default) -> 9 taps      (:1299-1301)        */
+  float eps;                               /* 1e-6                                            (:1292)             */
+} eegspec_cls_spec_params;
+
+void eegspec_cls_spec_params_default(eegspec_cls_spec_params *p);
+size_t eegspec_classifier_spec_workspace(int64_t batch, const eegspec_cls_spec_params *p);
+
+/* win: device fp32 (batch, rows, cols), NaNs allowed.  out: device (batch, 3, rows, cols) fp32, the three
+ * planes identical (np.tile).  status: device int32 (batch) or NULL; 1 = a row is entirely NaN (the reference
+ * drops it and resizes the image with scikit-image -- refused). */
+int eegspec_classifier_spec_f32(const float *win, int64_t batch, const eegspec_cls_spec_params *p, float *out,
+                                int32_t *status, void *workspace, size_t workspace_bytes, void *stream);
+
 /* Number of kernel launches issued by this library since load (bench bookkeeping). */
 int64_t eegspec_launch_count(void);
 

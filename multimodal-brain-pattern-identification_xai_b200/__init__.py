@@ -31,6 +31,9 @@ _API = {
     "install": "transform",
     "launch_count": "transform",
     "spectrogram_condition": "diffeeg",
+    "process_eeg": "classifier",
+    "process_spectrogram": "classifier",
+    "spectrogram_window": "classifier",
     "EEGTransformer": "eegtransformer",
     "xform_params": "eegtransformer",
     "eeg_transform_stft": "eegtransformer",

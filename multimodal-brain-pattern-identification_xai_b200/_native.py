@@ -53,6 +53,22 @@ class CondParams(C.Structure):
                 ("out_channels", C.c_int32), ("out_length", C.c_int32), ("mix_alpha", C.c_float)]
 
 
+CLS_MAX_TAPS = 13
+
+
+class ClsEegParams(C.Structure):
+    _fields_ = [("n_taps1", C.c_int32), ("b1", C.c_double * CLS_MAX_TAPS), ("a1", C.c_double * CLS_MAX_TAPS),
+                ("n_taps2", C.c_int32), ("b2", C.c_double * CLS_MAX_TAPS), ("a2", C.c_double * CLS_MAX_TAPS),
+                ("n_pairs", C.c_int32), ("pair_a", C.c_int32 * MAX_PAIRS), ("pair_b", C.c_int32 * MAX_PAIRS),
+                ("n_features", C.c_int32), ("fixed_length", C.c_int32), ("eps", C.c_float)]
+
+
+class ClsSpecParams(C.Structure):
+    _fields_ = [("rows", C.c_int32), ("cols", C.c_int32), ("notch_b", C.c_double * 3), ("notch_a", C.c_double * 3),
+                ("notch_zi", C.c_double * 2), ("gauss_sigma", C.c_float), ("gauss_truncate", C.c_float),
+                ("eps", C.c_float)]
+
+
 # name -> (restype, argtypes); mirrors include/eegspec.h one to one.
 SIGNATURES = {
     "eegspec_abi_version": (C.c_int, []),
@@ -93,6 +109,15 @@ SIGNATURES = {
                                                  C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
     "eegspec_spec_condition_f32": (C.c_int, [C.c_void_p, C.c_int64, C.POINTER(CondParams), C.c_void_p, C.c_void_p,
                                              C.c_void_p, C.c_void_p, C.c_void_p]),
+    "eegspec_cls_eeg_params_default": (None, [C.POINTER(ClsEegParams)]),
+    "eegspec_classifier_eeg_workspace": (C.c_size_t, [C.c_int64, C.c_int64, C.c_int32]),
+    "eegspec_classifier_eeg_f32": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, C.c_int32, C.c_int64,
+                                             C.POINTER(ClsEegParams), C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t,
+                                             C.c_void_p]),
+    "eegspec_cls_spec_params_default": (None, [C.POINTER(ClsSpecParams)]),
+    "eegspec_classifier_spec_workspace": (C.c_size_t, [C.c_int64, C.POINTER(ClsSpecParams)]),
+    "eegspec_classifier_spec_f32": (C.c_int, [C.c_void_p, C.c_int64, C.POINTER(ClsSpecParams), C.c_void_p, C.c_void_p,
+                                              C.c_void_p, C.c_size_t, C.c_void_p]),
     "eegspec_launch_count": (C.c_int64, []),
 }
 

@@ -20,7 +20,7 @@ LIB_PATH = os.path.join(LIB_DIR, "libeegspec.so")
 STAMP = os.path.join(LIB_DIR, "libeegspec.stamp")
 INCLUDE = os.path.join(os.path.dirname(PKG_DIR), "include")
 
-SOURCES = ["abi.cu", "stft_image.cu", "melspec.cu", "melspec_tc.cu", "melspec_ts.cu", "eegtransform.cu", "spec_condition.cu"]
+SOURCES = ["abi.cu", "stft_image.cu", "melspec.cu", "melspec_tc.cu", "melspec_ts.cu", "eegtransform.cu", "spec_condition.cu", "classifier_eeg.cu", "classifier_spec.cu"]
 NVCC_FLAGS = [
     "-O3", "-std=c++17",
     "-gencode", "arch=compute_100a,code=sm_100a",

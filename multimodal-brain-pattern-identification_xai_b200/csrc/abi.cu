@@ -367,6 +367,34 @@ int eegspec_spec_condition_f32(const float* spec, int64_t batch, const eegspec_c
   return spec_condition_launch(spec, batch, p, weight, bias, partner, out, static_cast<cudaStream_t>(stream));
 }
 
+void eegspec_cls_eeg_params_default(eegspec_cls_eeg_params* p) {
+  if (p) cls_eeg_params_default(p);
+}
+
+size_t eegspec_classifier_eeg_workspace(int64_t batch, int64_t length, int32_t n_ch) {
+  return cls_eeg_workspace(batch, length, n_ch);
+}
+
+int eegspec_classifier_eeg_f32(const float* x, int64_t batch, int64_t length, int32_t n_ch, int64_t rec_stride,
+                               const eegspec_cls_eeg_params* p, float* out, int32_t* status, void* workspace,
+                               size_t workspace_bytes, void* stream) {
+  return cls_eeg_launch(x, batch, length, n_ch, rec_stride, p, out, status, workspace, workspace_bytes,
+                        static_cast<cudaStream_t>(stream));
+}
+
+void eegspec_cls_spec_params_default(eegspec_cls_spec_params* p) {
+  if (p) cls_spec_params_default(p);
+}
+
+size_t eegspec_classifier_spec_workspace(int64_t batch, const eegspec_cls_spec_params* p) {
+  return cls_spec_workspace(batch, p);
+}
+
+int eegspec_classifier_spec_f32(const float* win, int64_t batch, const eegspec_cls_spec_params* p, float* out,
+                                int32_t* status, void* workspace, size_t workspace_bytes, void* stream) {
+  return cls_spec_launch(win, batch, p, out, status, workspace, workspace_bytes, static_cast<cudaStream_t>(stream));
+}
+
 int64_t eegspec_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 
 }  // extern "C"

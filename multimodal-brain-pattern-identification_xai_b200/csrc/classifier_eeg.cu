@@ -1,0 +1,397 @@
+// Row (f)4: the classifier-side EEG preprocessing -- the tensor the multimodal model's EEG branch (and the
+// SHAP GradientExplainer, XAI_Multimodality.py:2283-2290) receives.
+//
+// Replaces CombinedDataset.process_eeg, /root/reference/root/jupyter_notebooks/XAI_Multimodality.py:1148-1164,
+// with its helpers :1212-1286 (the same code as /root/reference/root/src/utils/data_utils.py:183-249):
+//   waves = eeg.values.T                                      (20, n)   :1151
+//   butter_bandpass_filter(0.5-20 Hz @ 200 Hz, order 5)       causal lfilter along time, zero state   :1156
+//   handle_nan                                                NaN -> nanmean of the (filtered) row     :1157
+//   calculate_differential_signals                            18 montage differences appended -> (38, n)
+//   denoise_filter                                            band-pass order 6, 4-tap forward mean (np.roll on the
+//                                                             FLATTENED array), every 4th sample -> (38, ~n/4)
+//   normalize                                                 per-row z-score, population std + 1e-6
+//   select_and_map_channels                                   rows 0..18 and 19..36 (EKG + the first 17 differences:
+//                                                             the differences start at row 20, the index at 19)
+//   pad_or_truncate(3000)                                     -> (1, 37, 3000) fp32
+//
+// What bounds it.  The two Butterworth band-passes are 10th / 12th order DIRECT-FORM recurrences with poles at
+// radius 0.995 / 0.998, run by the reference in float64.  They are so ill-conditioned (states ~1e12 times larger
+// than the output) that a 1e-12 relative change of the input moves the z-scored output by 0.08: the reference's
+// result is defined by its rounding sequence.  So this kernel executes SciPy's lfilter operation for operation
+// (df2t_step below: unfused multiplies and adds in SciPy's order -- bit-identical recurrences), takes the montage
+// differences BEFORE the second filter like the reference (filter(a) - filter(b) is not filter(a - b) at this
+// conditioning), and cannot cut a row into chunks.  20 first-filter and 38 second-filter recurrences per record,
+// ~2 000 double-precision operations per sample: FP64-pipe bound (64 lanes per SM), not HBM bound.
+//   kernel 1  one warp per record, one pass over time.  Lanes 0..19 = the parquet columns: first filter + NaN
+//             fill (a NaN turns the rest of a filtered row into NaN, so the fill value -- the nanmean of the row --
+//             is the mean of the prefix, known on the spot).  Every lane then owns row `lane` of the 38-row array
+//             (lanes 0..5 also row 32 + lane): channel rows use their own value, difference rows fetch the two
+//             channels by shuffle; second filter, 4-tap mean + decimation, float4 stores into the workspace.
+//   kernel 2  CTA = (record, output row): mean / std in double precision (two passes over L2-resident data, like
+//             NumPy), z-score, zero padding to 3000.
+#include <math.h>
+#include <string.h>
+
+#include "common.cuh"
+#include "internal.h"
+
+namespace eegspec {
+
+constexpr int kClsMaxTaps = EEGSPEC_CLS_MAX_TAPS;   // 13
+
+struct ClsFilterArgs {
+  const float* x;        // (batch, n, n_ch) time-major
+  float* dec;            // workspace: (batch, n_rows_all, dec_pitch) decimated second-filter output (in-row terms of the 4-tap mean)
+  double* head;          // workspace: (batch, n_rows_all, 4) first second-filter outputs of every row (for the wrap)
+  int* status;           // (batch) or null: 1 = a filtered row is all NaN (the reference drops it)
+  long long rec_stride, n, n_dec, dec_pitch;
+  int n_ch, n_rows_all;  // n_rows_all = n_ch + n_pairs rows of the reference's stacked array
+  int src_a[64], src_b[64];   // row r: lane of its minuend / subtrahend channel (src_b < 0: a channel row)
+  double b1[kClsMaxTaps], a1[kClsMaxTaps], b2[kClsMaxTaps], a2[kClsMaxTaps];
+};
+
+// One direct-form-II-transposed step, in EXACTLY the operation order of SciPy's lfilter (scipy/signal/
+// _lfilter.c.in, double_filt): y = z0 + b0 x;  z_i = (z_{i+1} + x b_{i+1}) - y a_{i+1};  z_last = x b - y a, every
+// product and sum rounded on its own (no FMA).  This is not pedantry: the reference's direct-form 10th / 12th order
+// band-passes are so ill-conditioned (states ~1e12 times larger than the output) that a 1e-12 relative change of
+// the input moves the z-scored output by 0.08 -- the reference's result is defined by its rounding sequence, and
+// fused multiply-adds gave 4e-2 of disagreement.  With the same sequence the recurrences are bit-identical to
+// SciPy's.  SKIP: odd numerator taps are zero (Butterworth band-pass); x * 0 + z == z exactly, so they are dropped.
+template <int N, bool SKIP>
+__device__ __forceinline__ double df2t_step(const double (&b)[kClsMaxTaps], const double (&a)[kClsMaxTaps],
+                                            double (&z)[kClsMaxTaps - 1], double x) {
+  const double y = __dadd_rn(z[0], __dmul_rn(b[0], x));
+#pragma unroll
+  for (int i = 0; i < N - 2; ++i) {
+    const double t = (SKIP && ((i + 1) & 1)) ? z[i + 1] : __dadd_rn(z[i + 1], __dmul_rn(x, b[i + 1]));
+    z[i] = __dsub_rn(t, __dmul_rn(y, a[i + 1]));
+  }
+  z[N - 2] = __dsub_rn((SKIP && ((N - 1) & 1)) ? 0.0 : __dmul_rn(x, b[N - 1]), __dmul_rn(y, a[N - 1]));
+  return y;
+}
+
+// np.nanmean(row) = np.sum(row with NaN -> 0) / count, and np.sum over a contiguous row is NumPy's PAIRWISE
+// summation: blocks of <= 128 elements summed with 8 strided accumulators, combined as ((r0+r1)+(r2+r3))+((r4+r5)+
+// (r6+r7)), a block remainder added one by one, blocks combined by recursive halving (left half rounded down to a
+// multiple of 8).  The fill value feeds the ill-conditioned second filter, so it has to be that sum to the last bit.
+// The tree only depends on the row length: its traversal is uniform across the warp.  Every block starts at a
+// multiple of 8, so accumulator index = sample index mod 8.
+constexpr int kPwBlock = 128, kPwDepth = 40;
+struct PairwiseWalk {            // uniform: where in NumPy's recursion the current sample sits
+  long long len[kPwDepth];       // frame: length of the segment
+  unsigned char right[kPwDepth]; // frame: 1 = its left half is done (value on the lane's stack), now in the right half
+  int depth;                     // frames in use; the top frame is the current leaf
+  long long leaf_left;           // samples of the current leaf still to come
+  __device__ void descend() {
+    while (len[depth - 1] > kPwBlock) {
+      long long n2 = len[depth - 1] / 2;
+      n2 -= n2 % 8;
+      len[depth] = n2;
+      right[depth] = 0;
+      ++depth;
+    }
+    leaf_left = len[depth - 1];
+  }
+};
+__device__ __forceinline__ double pw_combine(const double (&r)[8]) {
+  return __dadd_rn(__dadd_rn(__dadd_rn(r[0], r[1]), __dadd_rn(r[2], r[3])), __dadd_rn(__dadd_rn(r[4], r[5]), __dadd_rn(r[6], r[7])));
+}
+
+template <int N1, int N2, bool SKIP>
+__global__ void __launch_bounds__(32) classifier_eeg_filter_kernel(const ClsFilterArgs a) {
+  const int lane = threadIdx.x;
+  const long long rec = blockIdx.x;
+  const long long n = a.n;
+  const int nc = a.n_ch;
+  const bool is_ch = lane < nc;
+  const float* xp = a.x + rec * a.rec_stride + (is_ch ? lane : 0);
+  // rows of this lane: r0 = lane, r1 = 32 + lane (when they exist)
+  const int r0 = lane, r1 = 32 + lane;
+  const bool has0 = r0 < a.n_rows_all, has1 = r1 < a.n_rows_all;
+  const int sa0 = has0 ? a.src_a[r0] : 0, sb0 = has0 ? a.src_b[r0] : -1;
+  const int sa1 = has1 ? a.src_a[r1] : 0, sb1 = has1 ? a.src_b[r1] : -1;
+  const bool any1 = a.n_rows_all > 32;
+  float* dp0 = a.dec + (rec * a.n_rows_all + r0) * a.dec_pitch;
+  float* dp1 = a.dec + (rec * a.n_rows_all + r1) * a.dec_pitch;
+  double z1[kClsMaxTaps - 1], z2a[kClsMaxTaps - 1], z2b[kClsMaxTaps - 1];
+#pragma unroll
+  for (int i = 0; i < kClsMaxTaps - 1; ++i) z1[i] = z2a[i] = z2b[i] = 0.0;
+  double fill = 0.0;
+  bool filled = false;
+  // pairwise-sum state of this lane's first-filter output (see above)
+  PairwiseWalk walk;
+  walk.depth = 1;
+  walk.len[0] = n;
+  walk.right[0] = 0;
+  walk.descend();
+  double pr[8], pres = 0.0, pstack[kPwDepth];
+  int psp = 0;
+  bool in_rest = false;          // uniform: the leaf's last (len % 8) samples are added to pres one by one
+#pragma unroll
+  for (int j = 0; j < 8; ++j) pr[j] = 0.0;
+
+  float xn[8];   // the next eight samples are loaded while the current eight run through the recurrences
+#pragma unroll
+  for (int k = 0; k < 8; ++k) xn[k] = (is_ch && k < n) ? __ldg(xp + (long long)k * nc) : 0.f;
+  float4 q0 = make_float4(0.f, 0.f, 0.f, 0.f), q1 = q0;
+  for (long long t0 = 0; t0 < n; t0 += 8) {
+    float xc[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      xc[k] = xn[k];
+      const long long t = t0 + 8 + k;
+      xn[k] = (is_ch && t < n) ? __ldg(xp + t * nc) : 0.f;
+    }
+    if (!in_rest && walk.leaf_left < 8) {   // uniform: fewer than 8 samples left in the leaf -> the sequential rest
+      pres = pw_combine(pr);
+      in_rest = true;
+    }
+    double acc[2][2] = {{0.0, 0.0}, {0.0, 0.0}};   // [decimated sample of this iteration][row slot]
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      if (t0 + k < n) {                       // uniform across the warp
+        double y1 = 0.0;
+        if (is_ch) {
+          if (!filled) {
+            y1 = df2t_step<N1, SKIP>(a.b1, a.a1, z1, (double)xc[k]);
+            if (y1 != y1) {   // the rest of this filtered row is NaN: nanmean = pairwise sum of the prefix / its length
+              filled = true;
+              const long long t = t0 + k;
+              if (t == 0) {
+                if (a.status) a.status[rec] = 1;
+              } else {
+                double cur = in_rest ? pres : pw_combine(pr);
+                int sp = psp;
+                for (int d = walk.depth - 2; d >= 0; --d)     // up the recursion: finished left halves are added
+                  if (walk.right[d]) cur = __dadd_rn(pstack[--sp], cur);
+                fill = cur / (double)t;
+              }
+              y1 = fill;
+            } else if (in_rest) {
+              pres = __dadd_rn(pres, y1);
+            } else {
+              pr[k] = __dadd_rn(pr[k], y1);
+            }
+          } else {
+            y1 = fill;
+          }
+        }
+        // row inputs: a channel row is the lane's own value, a difference row fetches its two channels
+        const double va0 = __shfl_sync(0xffffffffu, y1, sa0), vb0 = __shfl_sync(0xffffffffu, y1, sb0 < 0 ? 0 : sb0);
+        const double u0 = sb0 < 0 ? va0 : __dsub_rn(va0, vb0);
+        if (has0) {
+          const double y2 = df2t_step<N2, SKIP>(a.b2, a.a2, z2a, u0);
+          if (t0 + k < 3) a.head[(rec * a.n_rows_all + r0) * 4 + t0 + k] = y2;
+          acc[k >> 2][0] = __dadd_rn(acc[k >> 2][0], y2);
+        }
+        if (any1) {                           // uniform
+          const double va1 = __shfl_sync(0xffffffffu, y1, sa1), vb1 = __shfl_sync(0xffffffffu, y1, sb1 < 0 ? 0 : sb1);
+          const double u1 = sb1 < 0 ? va1 : __dsub_rn(va1, vb1);
+          if (has1) {
+            const double y2 = df2t_step<N2, SKIP>(a.b2, a.a2, z2b, u1);
+            if (t0 + k < 3) a.head[(rec * a.n_rows_all + r1) * 4 + t0 + k] = y2;
+            acc[k >> 2][1] = __dadd_rn(acc[k >> 2][1], y2);
+          }
+        }
+      }
+    }
+    // ---- pairwise walk (uniform): these 8 samples (or the row's last few) are consumed
+    {
+      const long long used = min(8LL, min(walk.leaf_left, n - t0));
+      walk.leaf_left -= used;
+      if (walk.leaf_left == 0 && t0 + used < n) {   // leaf complete and more samples follow: climb, then descend
+        double cur = in_rest ? pres : pw_combine(pr);
+        in_rest = false;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) pr[j] = 0.0;
+        --walk.depth;                                // pop the leaf
+        while (walk.depth > 0 && walk.right[walk.depth - 1]) {   // finished a right half: left + right
+          cur = __dadd_rn(pstack[--psp], cur);
+          --walk.depth;
+        }
+        // finished the left half of the top frame: keep its sum, go into the right half
+        pstack[psp++] = cur;
+        long long n2 = walk.len[walk.depth - 1] / 2;
+        n2 -= n2 % 8;
+        walk.right[walk.depth - 1] = 1;
+        walk.len[walk.depth] = walk.len[walk.depth - 1] - n2;
+        walk.right[walk.depth] = 0;
+        ++walk.depth;
+        walk.descend();
+      }
+    }
+    // decimated samples m = t0 / 4 and m + 1 exist when their first term does (y[:, 0:-1:4]: t < n - 1); terms
+    // beyond the row's end come from the NEXT row of the flattened array and are added by the second kernel
+    const long long m = t0 >> 2;            // even
+    const bool e0 = t0 < n - 1, e1 = t0 + 4 < n - 1;
+    if (e0) {
+      const float v00 = (float)(acc[0][0] * 0.25), v01 = (float)(acc[0][1] * 0.25);
+      const float v10 = (float)(acc[1][0] * 0.25), v11 = (float)(acc[1][1] * 0.25);
+      if ((m & 2) == 0) { q0.x = v00; q1.x = v01; q0.y = v10; q1.y = v11; }
+      else { q0.z = v00; q1.z = v01; q0.w = v10; q1.w = v11; }
+      const long long m_last = e1 ? m + 1 : m;
+      if ((m & 2) || m_last == a.n_dec - 1) {
+        if (has0) *reinterpret_cast<float4*>(dp0 + (m & ~3LL)) = q0;
+        if (has1) *reinterpret_cast<float4*>(dp1 + (m & ~3LL)) = q1;
+      }
+    }
+  }
+}
+
+struct ClsFinishArgs {
+  const float* dec;
+  const double* head;
+  float* out;            // (batch, 1, n_rows, fixed_length)
+  long long n, n_dec, dec_pitch;
+  int n_rows_all, n_rows, fixed_length;
+  float eps;
+};
+
+__device__ __forceinline__ double block_sum(double v, double* red) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  __syncthreads();
+  if (lane == 0) red[warp] = v;
+  __syncthreads();
+  double s = 0.0;
+  for (int w = 0; w < (int)(blockDim.x >> 5); ++w) s += red[w];
+  return s;
+}
+
+__global__ void __launch_bounds__(256) classifier_eeg_finish_kernel(const ClsFinishArgs a) {
+  __shared__ double red[8];
+  // Output row o is row o of the reference's stacked array: rows 0 .. n_feat - 1 are kept, then
+  // select_and_map_channels continues at index n_feat (= 19: EKG and the first 17 differences) -- one sequence.
+  const int r = blockIdx.x;
+  const long long rec = blockIdx.y;
+  const float* d = a.dec + (rec * a.n_rows_all + r) * a.dec_pitch;
+  // the 4-tap mean of the last decimated sample may reach past the row's end: np.roll rolled the FLATTENED
+  // array, so those terms are the first samples of the next row
+  const long long t_last = 4 * (a.n_dec - 1);
+  const int spill = (int)(t_last + 4 - a.n);       // 0 .. 2 terms taken from the next row
+  double wrap = 0.0;
+  for (int k = 0; k < spill; ++k) wrap += a.head[(rec * a.n_rows_all + r + 1) * 4 + k];
+  wrap *= 0.25;
+  auto value = [&](long long m) { return (double)d[m] + (m == a.n_dec - 1 ? wrap : 0.0); };
+  double s = 0.0;
+  for (long long m = threadIdx.x; m < a.n_dec; m += blockDim.x) s += value(m);
+  const double mean = block_sum(s, red) / (double)a.n_dec;
+  double s2 = 0.0;
+  for (long long m = threadIdx.x; m < a.n_dec; m += blockDim.x) { const double e = value(m) - mean; s2 += e * e; }
+  const double sd = sqrt(block_sum(s2, red) / (double)a.n_dec);
+  const double inv = 1.0 / (sd + (double)a.eps);
+  float* op = a.out + (rec * a.n_rows + r) * a.fixed_length;
+  for (int m = threadIdx.x; m < a.fixed_length; m += blockDim.x)
+    op[m] = m < a.n_dec ? (float)((value(m) - mean) * inv) : 0.f;
+}
+
+// butter(5 / 6, [0.5, 20] / 100, btype='band') of SciPy, the reference's configuration (XAI_Multimodality.py:205,
+// :1156, :1268); tests/test_oracle_classifier.py checks them against scipy.signal.butter.
+void cls_eeg_params_default(eegspec_cls_eeg_params* p) {
+  memset(p, 0, sizeof(*p));
+  static const double b1[11] = {0.001151186385343785, 0.0, -0.005755931926718925, 0.0, 0.01151186385343785, 0.0,
+                                -0.01151186385343785, 0.0, 0.005755931926718925, 0.0, -0.001151186385343785};
+  static const double a1[11] = {1.0, -7.984802744723613, 28.780856801970636, -61.73788169912945, 87.3622028993991,
+                                -85.26668263284571, 58.15374986122678, -27.370865501025044, 8.508305070326013,
+                                -1.5772751257927395, 0.13239307063386374};
+  static const double b2[13] = {0.00029907903377907595, 0.0, -0.0017944742026744557, 0.0, 0.004486185506686139, 0.0,
+                                -0.005981580675581519, 0.0, 0.004486185506686139, 0.0, -0.0017944742026744557, 0.0,
+                                0.00029907903377907595};
+  static const double a2[13] = {1.0, -9.590565799057455, 42.26925892991835, -113.28827916089676, 205.76645819090106,
+                                -266.95101519796117, 253.7409420393535, -178.0830856181304, 91.60031314619462,
+                                -33.67762836365999, 8.400738521120699, -1.276480884387838, 0.08934419660572798};
+  p->n_taps1 = 11;
+  p->n_taps2 = 13;
+  for (int i = 0; i < 11; ++i) { p->b1[i] = b1[i]; p->a1[i] = a1[i]; }
+  for (int i = 0; i < 13; ++i) { p->b2[i] = b2[i]; p->a2[i] = a2[i]; }
+  // CFG.map_features over CFG.feature_to_index (XAI_Multimodality.py:211-224)
+  static const int pa[18] = {0, 4, 5, 6, 0, 1, 2, 3, 11, 15, 16, 17, 11, 12, 13, 14, 8, 9};
+  static const int pb[18] = {4, 5, 6, 7, 1, 2, 3, 7, 15, 16, 17, 18, 12, 13, 14, 18, 9, 10};
+  p->n_pairs = 18;
+  for (int i = 0; i < 18; ++i) { p->pair_a[i] = pa[i]; p->pair_b[i] = pb[i]; }
+  p->n_features = 19;
+  p->fixed_length = 3000;
+  p->eps = 1e-6f;
+}
+
+static long long cls_n_dec(long long n) { return n >= 2 ? (n - 2) / 4 + 1 : 0; }   // len(range(0, n - 1, 4))
+
+size_t cls_eeg_workspace(long long batch, long long length, int n_ch) {
+  if (batch <= 0 || length < 2 || n_ch <= 0) return 0;
+  const long long pitch = (cls_n_dec(length) + 3) & ~3LL;
+  const long long rows = n_ch + EEGSPEC_MAX_PAIRS;      // an upper bound: the pair count is a run-time parameter
+  return (size_t)batch * rows * ((size_t)pitch * sizeof(float) + 4 * sizeof(double));
+}
+
+int cls_eeg_launch(const float* x, long long batch, long long length, int n_ch, long long rec_stride,
+                   const eegspec_cls_eeg_params* p, float* out, int* status, void* workspace, size_t workspace_bytes,
+                   cudaStream_t st) {
+  if (!x || !out || !p || batch <= 0 || n_ch <= 0) return EEGSPEC_EINVAL;
+  if (length < 2) return EEGSPEC_ESHORT;
+  if (rec_stride < length * n_ch) return EEGSPEC_EINVAL;
+  if (p->n_taps1 != 11 || p->n_taps2 != 13) return EEGSPEC_EUNSUPPORTED;   // orders 5 and 6, the reference's
+  if (p->n_pairs < 1 || p->n_pairs > EEGSPEC_MAX_PAIRS || p->n_features < 1 || p->n_features > n_ch) return EEGSPEC_EINVAL;
+  if (n_ch > 32) return EEGSPEC_EUNSUPPORTED;                               // one lane per parquet column
+  if (p->fixed_length < 1) return EEGSPEC_EINVAL;
+  if (fabs(p->a1[0] - 1.0) > 1e-12 || fabs(p->a2[0] - 1.0) > 1e-12) return EEGSPEC_EINVAL;
+  for (int i = 0; i < p->n_pairs; ++i)
+    if (p->pair_a[i] < 0 || p->pair_a[i] >= n_ch || p->pair_b[i] < 0 || p->pair_b[i] >= n_ch) return EEGSPEC_EINVAL;
+  if (batch > 65535) return EEGSPEC_EUNSUPPORTED;
+  const size_t need = cls_eeg_workspace(batch, length, n_ch);
+  if (!workspace || workspace_bytes < need) return EEGSPEC_EWORKSPACE;
+  if (reinterpret_cast<uintptr_t>(workspace) & 15) return EEGSPEC_EALIGN;
+  const int n_rows_all = n_ch + p->n_pairs, n_rows = p->n_features + p->n_pairs;
+  // output row o is row o of the stacked array and its 4-tap mean may reach into row o + 1
+  if (n_rows > n_rows_all - 1) return EEGSPEC_EINVAL;
+
+  ClsFilterArgs f;
+  f.x = x;
+  f.rec_stride = rec_stride;
+  f.n = length;
+  f.n_dec = cls_n_dec(length);
+  f.dec_pitch = (f.n_dec + 3) & ~3LL;
+  f.n_ch = n_ch;
+  f.n_rows_all = n_rows_all;
+  for (int r = 0; r < 64; ++r) {
+    f.src_a[r] = r < n_ch ? r : (r < n_rows_all ? p->pair_a[r - n_ch] : 0);
+    f.src_b[r] = r < n_ch ? -1 : (r < n_rows_all ? p->pair_b[r - n_ch] : -1);
+  }
+  f.head = static_cast<double*>(workspace);                                   // 8-byte data first
+  f.dec = reinterpret_cast<float*>(f.head + (size_t)batch * n_rows_all * 4);
+  f.status = status;
+  bool skip = true;
+  for (int i = 0; i < kClsMaxTaps; ++i) {
+    f.b1[i] = i < p->n_taps1 ? p->b1[i] : 0.0;
+    f.a1[i] = i < p->n_taps1 ? p->a1[i] : 0.0;
+    f.b2[i] = i < p->n_taps2 ? p->b2[i] : 0.0;
+    f.a2[i] = i < p->n_taps2 ? p->a2[i] : 0.0;
+    if ((i & 1) && (f.b1[i] != 0.0 || f.b2[i] != 0.0)) skip = false;
+  }
+  if (status) {
+    const cudaError_t e = cudaMemsetAsync(status, 0, sizeof(int) * (size_t)batch, st);
+    if (e != cudaSuccess) return (int)e;
+  }
+  if (skip) classifier_eeg_filter_kernel<11, 13, true><<<(unsigned)batch, 32, 0, st>>>(f);
+  else classifier_eeg_filter_kernel<11, 13, false><<<(unsigned)batch, 32, 0, st>>>(f);
+  count_launch();
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return (int)e;
+
+  ClsFinishArgs g;
+  g.dec = f.dec;
+  g.head = f.head;
+  g.out = out;
+  g.n = length;
+  g.n_dec = f.n_dec;
+  g.dec_pitch = f.dec_pitch;
+  g.n_rows_all = n_rows_all;
+  g.n_rows = n_rows;
+  g.fixed_length = p->fixed_length;
+  g.eps = p->eps;
+  classifier_eeg_finish_kernel<<<dim3((unsigned)n_rows, (unsigned)batch), 256, 0, st>>>(g);
+  count_launch();
+  return (int)cudaGetLastError();
+}
+
+}  // namespace eegspec

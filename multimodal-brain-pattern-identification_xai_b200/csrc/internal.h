@@ -44,6 +44,17 @@ int melspec_sliding_launch(const float* eeg, int n_ch, long long total_length, l
 int spec_condition_launch(const float* spec, long long batch, const eegspec_cond_params* p, const float* weight,
                           const float* bias, const int* partner, float* out, cudaStream_t st);
 
+// classifier_eeg.cu / classifier_spec.cu
+void cls_eeg_params_default(eegspec_cls_eeg_params* p);
+size_t cls_eeg_workspace(long long batch, long long length, int n_ch);
+int cls_eeg_launch(const float* x, long long batch, long long length, int n_ch, long long rec_stride,
+                   const eegspec_cls_eeg_params* p, float* out, int* status, void* workspace, size_t workspace_bytes,
+                   cudaStream_t st);
+void cls_spec_params_default(eegspec_cls_spec_params* p);
+size_t cls_spec_workspace(long long batch, const eegspec_cls_spec_params* p);
+int cls_spec_launch(const float* win, long long batch, const eegspec_cls_spec_params* p, float* out, int* status,
+                    void* workspace, size_t workspace_bytes, cudaStream_t st);
+
 // eegtransform.cu
 void xform_params_default(eegspec_xform_params* p);
 long long xform_out_length(long long length, const eegspec_xform_params* p);

@@ -196,3 +196,55 @@ def load_reference_diffeeg(n_channels: int = 19, hidden_channels: int = 32, n_cl
                           diffEEG_trainer={"n_classes": n_classes, "n_channels": n_channels,
                                            "hidden_channels": hidden_channels, "dropout": dropout})
     return env["DiffEEG"](cfg)
+
+
+# --------------------------------------------------------------------------- classifier-side dataset (rows f3, f4)
+_NOTEBOOK = os.path.join(REFERENCE_ROOT, "root", "jupyter_notebooks", "XAI_Multimodality.py")
+
+
+def load_reference_combined_dataset(eeg_frames=None, spectrogram_frames=None):
+    """An instance of the reference's ``CombinedDataset`` (/root/reference/root/jupyter_notebooks/
+    XAI_Multimodality.py:1114-1307) with its own ``CFG`` class (:93-260), both lifted from the notebook export.
+    ``__init__`` is bypassed (it seeds RNGs and wants a metadata frame); the two loaders the methods call,
+    ``load_train_eeg_frame`` / ``load_train_spectr_frame`` (:480-503), are replaced by look-ups in the given
+    ``{id: DataFrame}`` dictionaries.  ``process_eeg(row)`` (:1148-1164) and ``process_spectrogram(row)``
+    (:1166-1204) then run exactly as in the notebook.  ``resize`` (scikit-image, not installed here) is the
+    identity for an image that already has the target shape -- the only case the fixtures exercise."""
+    import random
+
+    import numpy as np
+    import pandas as pd
+    import torch
+    from scipy.ndimage import gaussian_filter
+    from scipy.signal import butter, filtfilt, iirnotch, lfilter
+    from torch.utils.data import Dataset
+
+    def resize(sig, target_shape, mode="reflect", anti_aliasing=True):
+        if tuple(sig.shape) != tuple(target_shape):
+            raise NotImplementedError("skimage.transform.resize is not installed: only the identity case runs here")
+        return sig
+
+    def labels_to_probabilities(labels, num_classes):   # :630-632
+        return torch.eye(num_classes)[labels]
+
+    env = {"np": np, "pd": pd, "torch": torch, "random": random, "os": os, "Dataset": Dataset, "butter": butter,
+           "lfilter": lfilter, "filtfilt": filtfilt, "iirnotch": iirnotch, "gaussian_filter": gaussian_filter,
+           "resize": resize, "labels_to_probabilities": labels_to_probabilities,
+           "load_train_eeg_frame": lambda i: (eeg_frames or {})[int(i)],
+           "load_train_spectr_frame": lambda i: (spectrogram_frames or {})[int(i)]}
+    with open(_NOTEBOOK, "r", encoding="utf-8") as fh:
+        tree = ast.parse(fh.read(), filename=_NOTEBOOK)
+    wanted = {"CFG": None, "CombinedDataset": None}
+    for node in tree.body:                      # the FIRST definition of each (the export repeats some cells)
+        if isinstance(node, ast.ClassDef) and node.name in wanted and wanted[node.name] is None:
+            wanted[node.name] = node
+    module = ast.Module(body=[wanted["CFG"], wanted["CombinedDataset"]], type_ignores=[])
+    ast.fix_missing_locations(module)
+    exec(compile(module, _NOTEBOOK, "exec"), env)  # noqa: S102 - the reference's own code
+    cls = env["CombinedDataset"]
+    ds = cls.__new__(cls)
+    ds.cfg = env["CFG"]
+    ds.training_flag, ds.augmentations, ds.plot = False, None, False
+    ds.feature_to_index = ds.cfg.feature_to_index                         # :1126-1127
+    ds.differential_channels_start_index = len(ds.feature_to_index)
+    return ds

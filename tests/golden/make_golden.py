@@ -323,10 +323,58 @@ def make_diffeeg():
     print("wrote", path, os.path.getsize(path), "bytes")
 
 
+CLASSIFIER_EEG_CASES = {"clean": (10000, "clean"), "nan": (10400, "nan"), "long": (13000, "clean"), "odd": (10001, "nan")}
+
+
+def classifier_eeg_input(gold, name):
+    x = gold[f"eeg/{name}/x_i16"].astype(np.float32)
+    x[gold[f"eeg/{name}/x_i16"] == -32768] = np.nan
+    return x
+CLASSIFIER_SPEC_CASES = {"offset40": (320, 40), "no_offset_short": (250, None), "offset_near_end": (310, 250)}
+
+
+def make_classifier():
+    """``classifier_golden.npz``: inputs and outputs of the REFERENCE's own ``CombinedDataset.process_eeg`` and
+    ``process_spectrogram`` (/root/reference/root/jupyter_notebooks/XAI_Multimodality.py:1148-1204), lifted from
+    the notebook export by ``oracle/ref_extract.py``; pins rows (f)3 and (f)4."""
+    import pandas as pd
+    import scipy
+
+    rng = np.random.default_rng(20261108)
+    out = {}
+    for name, (n_pts, kind) in CLASSIFIER_EEG_CASES.items():
+        x = np.round(eeg_like(rng, (20, n_pts), walk=0.5, noise=6.0)).T.copy()       # (n, 20) integer microvolts
+        if kind == "nan":
+            x[n_pts // 2:n_pts // 2 + 25, 3] = np.nan          # everything after it is NaN after the first filter
+            x[rng.random(n_pts) < 0.002, 7] = np.nan
+            x[n_pts - 1, 12] = np.nan                          # the very last sample
+        ds = rx.load_reference_combined_dataset({1: pd.DataFrame(x, columns=mo.EEG_COLUMNS)}, {})
+        out[f"eeg/{name}/x_i16"] = np.where(np.isnan(x), -32768, x).astype(np.int16)   # NaN -> -32768 (see classifier_eeg_input)
+        out[f"eeg/{name}/y"] = ds.process_eeg({"eeg_id": 1}).numpy()
+    for name, (n_rows, offset) in CLASSIFIER_SPEC_CASES.items():
+        raw = rng.gamma(2.0, 8.0, size=(n_rows, 401)).astype(np.float16).astype(np.float32)   # positive power, fp16-exact
+        raw[:, 0] = np.arange(n_rows) * 2 + 1                                             # the 'time' column
+        raw[rng.random((n_rows, 401)) < 0.003] = np.nan
+        raw[40:60, 200] = np.nan
+        ds = rx.load_reference_combined_dataset({}, {2: pd.DataFrame(raw)})
+        row = {"spectrogram_id": 2}
+        if offset is not None:
+            row["spectrogram_label_offset_seconds"] = offset
+        y = ds.process_spectrogram(pd.Series(row) if offset is not None else row).numpy()
+        assert y.shape == (3, 400, 300) and np.array_equal(y[0], y[1]) and np.array_equal(y[0], y[2])
+        out[f"spec/{name}/raw_f16"] = raw.astype(np.float16)
+        out[f"spec/{name}/offset"] = np.array(-1 if offset is None else offset)
+        out[f"spec/{name}/y_plane"] = y[0]                      # the three planes are copies (np.tile, :1190)
+    out["versions"] = np.array([f"numpy {np.__version__}", f"scipy {scipy.__version__}", f"pandas {pd.__version__}"])
+    path = os.path.join(HERE, "classifier_golden.npz")
+    np.savez_compressed(path, **out)
+    print("wrote", path, os.path.getsize(path), "bytes")
+
+
 if __name__ == "__main__":
     if not rx.reference_available():
         raise SystemExit("/root/reference is not mounted: golden vectors can only be made in the build container")
     only = set(sys.argv[1:])
-    for fn in (make_stft, make_melspec, make_eegtransform, make_fronthalf, make_melspec_xcheck, make_diffeeg):
+    for fn in (make_stft, make_melspec, make_eegtransform, make_fronthalf, make_melspec_xcheck, make_diffeeg, make_classifier):
         if not only or fn.__name__ in only:
             fn()
