@@ -604,7 +604,18 @@ def main():
             c_r = arm.run("r10", arm.cores * 64, seed=5)
             c_r50 = arm.run("r50", arm.cores * 16, seed=6)
             c_xf = arm.run("xf", arm.cores * 32, seed=7)
+            c_next = {k: arm.run(k, n * arm.cores, seed=21) for k, n in (("f2", 2), ("f3", 16), ("f4", 8))} \
+                if "next_rows" in result else {}
             arm.close()
+            for k, name in (("f2", "f2_diffeeg_condition"), ("f3", "f3_process_spectrogram"), ("f4", "f4_process_eeg")):
+                if k in c_next and name in result["next_rows"]:
+                    result["next_rows"][name]["cpu_baseline"] = {
+                        "value": c_next[k]["records_per_s"], "unit": UNIT, "cores": arm.cores, "kind": "port",
+                        "sample": f"{c_next[k]['records']} records through oracle/"
+                                  + {"f2": "diffeeg_oracle.py (torch CPU conv_transpose2d + interpolate, 1 thread per worker)",
+                                     "f3": "classifier_oracle.py::process_spectrogram_oracle",
+                                     "f4": "classifier_oracle.py::process_eeg_oracle"}[k],
+                        "per_core": c_next[k]["per_core_records_per_s"]}
             if "eeg_transform" in result:
                 result["eeg_transform"]["cpu_baseline"] = {
                     "value": c_xf["records_per_s"], "unit": UNIT, "cores": arm.cores, "kind": "port",
@@ -684,12 +695,78 @@ def leg_eeg_transform(torch, b200spec, timed, keep, peak, world, args):
 
 
 def leg_next_rows(torch, b200spec, timed, keep, peak, world, args):
-    """Rows (f)2-(f)4 (filled in as they are built; absent entry points are skipped)."""
+    """Rows (f)2-(f)4: the consumer front end of DiffEEG and the classifier-side preprocessing."""
     out = {}
-    for name in ("bench_next_rows",):
-        fn = getattr(b200spec, name, None)
-        if fn is not None:
-            out.update(fn(timed=timed, keep=keep, peak=peak, world=world, steps=args.steps, roofline=roofline))
+    gen = torch.Generator(device="cuda").manual_seed(13)
+    steps = max(3, args.steps // 2)
+
+    # ---- (f)2: spectrogram condition of DiffEEG on the DiffEEG micro-batch and on 1 024 records
+    w = torch.randn((19, 16, 3, 3), device="cuda", generator=gen) * 0.1
+    b = torch.randn((16,), device="cuda", generator=gen) * 0.1
+    f2 = {"what": "DiffEEG.forward condition branch (diffEEG.py:47-53, 108-110): ConvTranspose2d(19->16, (3,3), stride (1,8)) "
+                  "-> relu -> flatten -> F.interpolate(2000) as ONE gather kernel; the (B,16,33,15991) intermediate is never formed"}
+    for batch, key in ((64, "diffeeg_batch"), (1024, "records1024")):
+        img = torch.rand((batch, 19, 33, 2000), device="cuda", generator=gen)
+        flush = torch.zeros(256 << 20 >> 2, device="cuda") if batch == 64 else None
+
+        def step_c():
+            keep["c"] = b200spec.spectrogram_condition(img, w, b, 2000)
+
+        ms, _ = timed(step_c, steps, 3, flush=flush)
+        keep.pop("c", None)
+        # bytes the operator has to touch: the 32-byte sectors of the gathered image values + the output
+        live = 1500 * 19 * 3 * 32                      # 3/8 of 4000 positions x C x 3 rows, one sector each
+        bytes_alg = batch * (live + 4 * 16 * 2000)
+        f2[key] = {"workload": f"({batch},19,33,2000) image -> ({batch},16,2000); "
+                               + ("L2 flushed between steps" if batch == 64 else "5.1 GB of images resident (> L2)"),
+                   "value": world * batch * steps / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms / steps,
+                   "roofline": roofline(bytes_alg, ms * 1e-3 / steps, peak,
+                                        "spec_condition_kernel; algorithmic bytes = 85 500 gathered image values as 32-byte "
+                                        "sectors (2.7 MB) + 128 KB out per record",
+                                        image_GBps_if_read_whole=batch * 4 * 19 * 33 * 2000 / (ms * 1e-3 / steps) / 1e9)}
+        del img, flush
+    out["f2_diffeeg_condition"] = f2
+
+    # ---- (f)4: classifier-side EEG preprocessing
+    x = torch.randn((RECORDS, 10000, 20), device="cuda", generator=gen).cumsum_(1).mul_(0.5)
+    x.add_(torch.randn((RECORDS, 10000, 20), device="cuda", generator=gen) * 5.0)
+
+    def step_e():
+        keep["e"] = b200spec.process_eeg(x, check=False)
+
+    ms, _ = timed(step_e, steps, 2)
+    keep.pop("e", None)
+    bytes_e = 4 * 10000 * 20 + 4 * 37 * 3000
+    out["f4_process_eeg"] = {
+        "what": "CombinedDataset.process_eeg (XAI_Multimodality.py:1148-1164): band-pass 5 -> NaN fill -> 18 differences -> "
+                "band-pass 6 + 4-tap mean + decimate 4 -> z-score -> (1,37,3000); SciPy-exact float64 recurrences "
+                "(20 + 38 per record): FP64-pipe bound, not HBM bound",
+        "workload": "(1024,10000,20) parquet rows -> (1024,1,37,3000)",
+        "value": world * RECORDS * steps / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms / steps,
+        "fp64_Gops_per_s": RECORDS * 10000 * (20 * 31 + 38 * 37) / (ms * 1e-3 / steps) / 1e9,
+        "roofline": roofline(RECORDS * bytes_e, ms * 1e-3 / steps, peak,
+                             f"classifier_eeg_filter_kernel + classifier_eeg_finish_kernel, {bytes_e} B/record")}
+    del x
+
+    # ---- (f)3: classifier-side spectrogram post-processing
+    win = torch.rand((RECORDS, 400, 300), device="cuda", generator=gen) * 40.0
+    win[:, 300:] = 0.0
+
+    def step_s():
+        keep["s"] = b200spec.process_spectrogram(win, check=False)
+
+    ms, _ = timed(step_s, steps, 2)
+    keep.pop("s", None)
+    bytes_s = 4 * 400 * 300 * 4
+    out["f3_process_spectrogram"] = {
+        "what": "CombinedDataset.process_spectrogram (XAI_Multimodality.py:1183-1202): NaN fill -> baseline -> 60 Hz notch "
+                "filtfilt -> Gaussian -> min-max -> 3 planes; four small kernels with fp32 intermediates",
+        "workload": "(1024,400,300) windows -> (1024,3,400,300)",
+        "value": world * RECORDS * steps / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms / steps,
+        "roofline": roofline(RECORDS * bytes_s, ms * 1e-3 / steps, peak,
+                             f"cls_spec_rowfill / column / row / planes kernels, {bytes_s} B/record algorithmic")}
+    del win
+    torch.cuda.empty_cache()
     return out
 
 

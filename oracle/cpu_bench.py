@@ -33,6 +33,13 @@ def synth_records(mode: str, n: int, seed: int) -> np.ndarray:
     rng = np.random.default_rng(seed)
     if mode == "xf":   # raw EEG, time-major (L, C) like the reference's parquet windows
         return (rng.standard_normal((n, 10000, 20), dtype=np.float32) * np.float32(40.0))
+    if mode == "f2":   # compute_stft images of the DiffEEG micro-batch
+        return rng.random((n, 19, 33, 2000), dtype=np.float32)
+    if mode == "f3":   # (400, 300) Kaggle-spectrogram windows
+        return rng.random((n, 400, 300), dtype=np.float32) * np.float32(40.0)
+    if mode == "f4":   # parquet rows (n, 20)
+        return (np.cumsum(rng.standard_normal((n, 10000, 20), dtype=np.float32), axis=1) * np.float32(0.5)
+                + rng.standard_normal((n, 10000, 20), dtype=np.float32) * np.float32(5.0))
     shape = (n, 20, 10000) if mode in ("n", "r50") else (n, 19, 2000)
     x = np.cumsum(rng.standard_normal(shape, dtype=np.float32), axis=-1) * np.float32(0.3)
     x += rng.standard_normal(shape, dtype=np.float32)
@@ -50,6 +57,23 @@ def _compute(mode: str, x: np.ndarray) -> float:
         from oracle import eegtransform_oracle
 
         out = eegtransform_oracle.eeg_transform_batch_oracle(x, n_feats=19, downsample=5)
+    elif mode == "f2":
+        import torch
+
+        from oracle import diffeeg_oracle
+
+        torch.set_num_threads(1)
+        g = torch.Generator().manual_seed(0)
+        w, b = torch.randn((19, 16, 3, 3), generator=g) * 0.1, torch.zeros(16)
+        out = diffeeg_oracle.spectrogram_condition_oracle(x, w, b, 2000).numpy()
+    elif mode == "f3":
+        from oracle import classifier_oracle
+
+        out = np.stack([classifier_oracle.process_spectrogram_oracle(r) for r in x])
+    elif mode == "f4":
+        from oracle import classifier_oracle
+
+        out = np.stack([classifier_oracle.process_eeg_oracle(r) for r in x])
     elif mode == "n":
         out = melspec_oracle.eeg_to_spectrogram_batch_oracle(x)
     else:
