@@ -160,6 +160,11 @@ int eegspec_stft_image_host_f32(const float *x, int64_t rows, int64_t length, in
 int eegspec_melspec_host_f32(const float *eeg, int64_t batch, int32_t n_ch, int64_t length,
                              const eegspec_mel_params *p, float *out, int device);
 
+/* Frees what the host-buffer front doors keep per device between calls (three streams and their staging
+ * buffers; they only grow otherwise).  Waits for the device's pipelines to drain first.  Safe to call at any
+ * time from any thread; the next host-buffer call on that device sets the pipeline up again. */
+int eegspec_release(int device);
+
 /* Bytes eegspec_melspec_host_f32 moves over PCIe for these arguments.  Channel-major records are
  * copied row-wise: only the electrode rows some pair of the montage reads travel (16 of the 20
  * EEG_COLUMNS rows for the HMS montage), the others are never touched on either side. */

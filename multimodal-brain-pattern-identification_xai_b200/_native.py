@@ -96,6 +96,7 @@ SIGNATURES = {
                                               C.c_int64, C.c_float, C.c_void_p, C.c_int]),
     "eegspec_melspec_host_f32": (C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_int64,
                                            C.POINTER(MelParams), C.c_void_p, C.c_int]),
+    "eegspec_release": (C.c_int, [C.c_int]),
     "eegspec_melspec_host_bytes": (C.c_int, [C.c_int64, C.c_int32, C.c_int64, C.POINTER(MelParams),
                                              C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
     "eegspec_xform_params_default": (None, [C.POINTER(XformParams)]),

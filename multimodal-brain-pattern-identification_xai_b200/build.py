@@ -48,7 +48,7 @@ def _sha(paths, extra=b"") -> str:
 
 
 def _headers():
-    return [os.path.join(CSRC, n) for n in sorted(os.listdir(CSRC)) if not n.endswith(".cu")] + \
+    return [os.path.join(CSRC, n) for n in sorted(os.listdir(CSRC)) if n.endswith((".h", ".cuh"))] + \
         [os.path.join(INCLUDE, "eegspec.h")]
 
 

@@ -25,8 +25,25 @@ struct HostPipe {
   void* buf[kPipeDepth][3] = {};   // in, out, workspace
   size_t cap[kPipeDepth][3] = {};
 };
-static std::mutex g_pipe_mu;
+static std::mutex g_pipe_mu[64];   // one per device: host-buffer calls on different devices do not serialise
 static HostPipe g_pipes[64];
+
+// Every early return of a host-buffer call goes through here: asynchronous copies into / out of the
+// caller's buffers may still be in flight on the pipeline streams, and the caller is about to free them.
+static int pipe_drain(HostPipe& p, int status) {
+  for (int s = 0; s < kPipeDepth; ++s) {
+    const cudaError_t e = cudaStreamSynchronize(p.stream[s]);
+    if (status == EEGSPEC_OK && e != cudaSuccess) status = (int)e;
+  }
+  return status;
+}
+
+// Restores the calling thread's current device on scope exit (the pipelines select `device`).
+struct DeviceGuard {
+  int prev = -1;
+  DeviceGuard() { if (cudaGetDevice(&prev) != cudaSuccess) prev = -1; }
+  ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
 
 static cudaError_t pipe_reserve(HostPipe& p, int slot, int which, size_t bytes) {
   if (bytes <= p.cap[slot][which]) return cudaSuccess;
@@ -194,7 +211,9 @@ int eegspec_stft_image_host_f32(const float* x, int64_t rows, int64_t length, in
   eegspec_stft_plan pl;
   int rc = stft_plan_make(length, nperseg, noverlap, out_cols, &pl);
   if (rc != EEGSPEC_OK) return rc;
-  std::lock_guard<std::mutex> lock(g_pipe_mu);
+  if (device < 0 || device >= 64) return EEGSPEC_EINVAL;
+  std::lock_guard<std::mutex> lock(g_pipe_mu[device]);
+  DeviceGuard restore;
   HostPipe* pipe = nullptr;
   if ((rc = pipe_open(device, &pipe)) != EEGSPEC_OK) return rc;
 
@@ -211,25 +230,21 @@ int eegspec_stft_image_host_f32(const float* x, int64_t rows, int64_t length, in
     const int s = n % kPipeDepth;
     const int64_t nr = rows - r0 < chunk ? rows - r0 : chunk;
     cudaError_t e;
-    if ((e = pipe_reserve(*pipe, s, 0, in_row * chunk)) != cudaSuccess) return (int)e;
-    if ((e = pipe_reserve(*pipe, s, 1, out_row * chunk)) != cudaSuccess) return (int)e;
-    if (ws_bytes && (e = pipe_reserve(*pipe, s, 2, ws_bytes)) != cudaSuccess) return (int)e;
+    if ((e = pipe_reserve(*pipe, s, 0, in_row * chunk)) != cudaSuccess) return pipe_drain(*pipe, (int)e);
+    if ((e = pipe_reserve(*pipe, s, 1, out_row * chunk)) != cudaSuccess) return pipe_drain(*pipe, (int)e);
+    if (ws_bytes && (e = pipe_reserve(*pipe, s, 2, ws_bytes)) != cudaSuccess) return pipe_drain(*pipe, (int)e);
     cudaStream_t st = pipe->stream[s];
     e = cudaMemcpyAsync(pipe->buf[s][0], x + r0 * length, in_row * nr, cudaMemcpyHostToDevice, st);
-    if (e != cudaSuccess) return (int)e;
+    if (e != cudaSuccess) return pipe_drain(*pipe, (int)e);
     rc = stft_image_launch(static_cast<const float*>(pipe->buf[s][0]), nr, length, length, nperseg,
                            noverlap, out_cols, eps, static_cast<float*>(pipe->buf[s][1]),
                            pipe->buf[s][2], pipe->cap[s][2], st);
-    if (rc != EEGSPEC_OK) return rc;
+    if (rc != EEGSPEC_OK) return pipe_drain(*pipe, rc);
     e = cudaMemcpyAsync(out + r0 * (int64_t)pl.n_freqs * out_cols, pipe->buf[s][1], out_row * nr,
                         cudaMemcpyDeviceToHost, st);
-    if (e != cudaSuccess) return (int)e;
+    if (e != cudaSuccess) return pipe_drain(*pipe, (int)e);
   }
-  for (int s = 0; s < kPipeDepth; ++s) {
-    cudaError_t e = cudaStreamSynchronize(pipe->stream[s]);
-    if (e != cudaSuccess) return (int)e;
-  }
-  return EEGSPEC_OK;
+  return pipe_drain(*pipe, EEGSPEC_OK);
 }
 
 int eegspec_melspec_host_f32(const float* eeg, int64_t batch, int32_t n_ch, int64_t length,
@@ -238,7 +253,12 @@ int eegspec_melspec_host_f32(const float* eeg, int64_t batch, int32_t n_ch, int6
   MelGeometry g;
   int rc = melspec_geometry(p, &g);
   if (rc != EEGSPEC_OK) return rc;
-  std::lock_guard<std::mutex> lock(g_pipe_mu);
+  if (length < p->crop) return EEGSPEC_ESHORT;            // everything melspec_launch would refuse is refused
+  for (int i = 0; i < p->n_chains * p->pairs_per_chain; ++i)   // BEFORE the first byte is copied
+    if (p->pair_a[i] < 0 || p->pair_a[i] >= n_ch || p->pair_b[i] < 0 || p->pair_b[i] >= n_ch) return EEGSPEC_EINVAL;
+  if (device < 0 || device >= 64) return EEGSPEC_EINVAL;
+  std::lock_guard<std::mutex> lock(g_pipe_mu[device]);
+  DeviceGuard restore;
   HostPipe* pipe = nullptr;
   if ((rc = pipe_open(device, &pipe)) != EEGSPEC_OK) return rc;
 
@@ -255,34 +275,52 @@ int eegspec_melspec_host_f32(const float* eeg, int64_t batch, int32_t n_ch, int6
     const int s = n % kPipeDepth;
     const int64_t nb = batch - r0 < chunk ? batch - r0 : chunk;
     cudaError_t e;
-    if ((e = pipe_reserve(*pipe, s, 0, in_rec * chunk)) != cudaSuccess) return (int)e;
-    if ((e = pipe_reserve(*pipe, s, 1, out_rec * chunk)) != cudaSuccess) return (int)e;
-    if ((e = pipe_reserve(*pipe, s, 2, ws_bytes)) != cudaSuccess) return (int)e;
+    if ((e = pipe_reserve(*pipe, s, 0, in_rec * chunk)) != cudaSuccess) return pipe_drain(*pipe, (int)e);
+    if ((e = pipe_reserve(*pipe, s, 1, out_rec * chunk)) != cudaSuccess) return pipe_drain(*pipe, (int)e);
+    if ((e = pipe_reserve(*pipe, s, 2, ws_bytes)) != cudaSuccess) return pipe_drain(*pipe, (int)e);
     cudaStream_t st = pipe->stream[s];
     if (n_runs == 0) {
       e = cudaMemcpyAsync(pipe->buf[s][0], eeg + r0 * (int64_t)n_ch * length, in_rec * nb,
                           cudaMemcpyHostToDevice, st);
-      if (e != cudaSuccess) return (int)e;
+      if (e != cudaSuccess) return pipe_drain(*pipe, (int)e);
     }
     for (int r = 0; r < n_runs; ++r) {   // only the electrode rows the montage reads: same layout, gaps left stale
       e = cudaMemcpy2DAsync(static_cast<float*>(pipe->buf[s][0]) + (int64_t)run_start[r] * length, in_rec,
                             eeg + (r0 * (int64_t)n_ch + run_start[r]) * length, in_rec,
                             (size_t)run_len[r] * length * sizeof(float), (size_t)nb, cudaMemcpyHostToDevice, st);
-      if (e != cudaSuccess) return (int)e;
+      if (e != cudaSuccess) return pipe_drain(*pipe, (int)e);
     }
     rc = melspec_launch(static_cast<const float*>(pipe->buf[s][0]), nb, n_ch, length,
                         (long long)n_ch * length, p, static_cast<float*>(pipe->buf[s][1]),
                         pipe->buf[s][2], pipe->cap[s][2], st);
-    if (rc != EEGSPEC_OK) return rc;
+    if (rc != EEGSPEC_OK) return pipe_drain(*pipe, rc);
     e = cudaMemcpyAsync(out + r0 * (int64_t)(out_rec / sizeof(float)), pipe->buf[s][1],
                         out_rec * nb, cudaMemcpyDeviceToHost, st);
-    if (e != cudaSuccess) return (int)e;
+    if (e != cudaSuccess) return pipe_drain(*pipe, (int)e);
   }
+  return pipe_drain(*pipe, EEGSPEC_OK);
+}
+
+int eegspec_release(int device) {
+  if (device < 0 || device >= 64) return EEGSPEC_EINVAL;
+  std::lock_guard<std::mutex> lock(g_pipe_mu[device]);
+  HostPipe& p = g_pipes[device];
+  if (!p.ready) return EEGSPEC_OK;
+  DeviceGuard restore;
+  cudaError_t e = cudaSetDevice(device);
+  if (e != cudaSuccess) return (int)e;
+  int status = pipe_drain(p, EEGSPEC_OK);
   for (int s = 0; s < kPipeDepth; ++s) {
-    cudaError_t e = cudaStreamSynchronize(pipe->stream[s]);
-    if (e != cudaSuccess) return (int)e;
+    for (int w = 0; w < 3; ++w) {
+      if (p.buf[s][w] && (e = cudaFree(p.buf[s][w])) != cudaSuccess && status == EEGSPEC_OK) status = (int)e;
+      p.buf[s][w] = nullptr;
+      p.cap[s][w] = 0;
+    }
+    if ((e = cudaStreamDestroy(p.stream[s])) != cudaSuccess && status == EEGSPEC_OK) status = (int)e;
+    p.stream[s] = nullptr;
   }
-  return EEGSPEC_OK;
+  p.ready = false;
+  return status;
 }
 
 int eegspec_melspec_host_bytes(int64_t batch, int32_t n_ch, int64_t length, const eegspec_mel_params* p,

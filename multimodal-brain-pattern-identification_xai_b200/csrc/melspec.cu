@@ -16,6 +16,7 @@
 //             {cos,sin} per thread), power, 2-tap sparse mel, 10 log10 -> scratch; pair maximum.
 //   kernel 2  dB referencing (needs the pair maximum), top_db clip, (x+40)/40, mean over the
 //             pairs of a chain, one float4 (4 chains) per (mel, time) pixel.
+#include <atomic>
 #include <math.h>
 
 #include <mutex>
@@ -677,7 +678,7 @@ int melspec_launch_strided(const float* eeg, long long batch, int n_ch, long lon
   if (!workspace || workspace_bytes < need) return EEGSPEC_EWORKSPACE;
   if (reinterpret_cast<uintptr_t>(workspace) & 15) return EEGSPEC_EALIGN;
 
-  static bool configured[64] = {};
+  static std::atomic<bool> configured[64];   // idempotent set-up; atomic so that concurrent callers do not race on the flag
   int dev = 0;
   cudaGetDevice(&dev);
   const size_t smem = pair_kernel_smem(*p);

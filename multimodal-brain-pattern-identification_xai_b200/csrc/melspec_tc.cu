@@ -21,6 +21,7 @@
 //     one thread  24 x tcgen05.mma (M=128, N=112, K=16), tcgen05.commit -> mbarrier
 //     all threads tcgen05.ld the 128 x 224 fp32 accumulators (lane = frame), power -> smem
 //     all threads sparse mel, 10 log10, store to scratch, running max      (as engine 1)
+#include <atomic>
 #include <cuda_fp16.h>
 
 #include "melspec_common.cuh"
@@ -368,7 +369,7 @@ size_t melspec_tc_smem_bytes(int crop) {
 }
 
 int melspec_tc_launch_pair(const MelArgs& a, int n_pairs, long long n_records, cudaStream_t st) {
-  static bool configured[64] = {};
+  static std::atomic<bool> configured[64];   // idempotent set-up; atomic so that concurrent callers do not race on the flag
   int dev = 0;
   cudaGetDevice(&dev);
   if (dev >= 0 && dev < 64 && !configured[dev]) {

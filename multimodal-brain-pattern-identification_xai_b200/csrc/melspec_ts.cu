@@ -31,6 +31,7 @@
 // Front half follows the reference (pair list /root/reference/root/config/config.yml:529-545,
 // differencing /root/reference/root/src/utils/data_utils.py:183-215, crop
 // /root/reference/root/src/utils/cfg_utils.py:369-371, NaN fill cfg_utils.py:380-385).
+#include <atomic>
 #ifdef EEGSPEC_TIMELINE   // debug builds only (tools/timeline_roles.py): clock stamps of the pipeline hand-offs
 #include <stdio.h>
 #include <stdlib.h>
@@ -768,7 +769,7 @@ size_t melspec_ts_smem_bytes() {
 int melspec_ts_run(const ChainArgs& a, long long clusters, cudaStream_t st) {
   if (a.n_chains != 4 || a.ppc != 4 || a.n_mels != 128 || a.n_time != 2 * kTileFrames) return EEGSPEC_EUNSUPPORTED;
   static std::mutex mu;
-  static bool configured[64] = {};
+  static std::atomic<bool> configured[64];   // idempotent set-up; atomic so that concurrent callers do not race on the flag
   int dev = 0;
   cudaGetDevice(&dev);
   if (dev < 0 || dev >= 64) return EEGSPEC_EUNSUPPORTED;

@@ -17,6 +17,8 @@
 //
 // HBM traffic is the algorithmic minimum: the row is read once (frames overlap in L1/L2),
 // the image is written once, nothing else touches DRAM.
+#include <atomic>
+
 #include "common.cuh"
 #include "internal.h"
 #include "stft_thread_fft.cuh"
@@ -652,7 +654,7 @@ size_t stft_image_workspace(long long rows, long long length, int nperseg, int n
 
 template <int LOG2N, int MODE>
 static int launch_mode(const StftArgs& a, long long grid, size_t smem, int threads, cudaStream_t st) {
-  static bool configured[64] = {};
+  static std::atomic<bool> configured[64];   // idempotent set-up; atomic so that concurrent callers do not race on the flag
   int dev = 0;
   cudaGetDevice(&dev);
   if (dev >= 0 && dev < 64 && !configured[dev]) {

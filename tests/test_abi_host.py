@@ -34,6 +34,28 @@ def test_every_declared_symbol_is_exported_and_bound():
 def test_struct_layout_matches_header():
     assert C.sizeof(nat.StftPlan) == 40
     assert C.sizeof(nat.MelParams) == 16 * 4 + 2 * 32 * 4 + 2 * 4
+    # eegspec_xform_params: int n_out, 2 x int[32], int, 2 floats, int (+4 pad), 2 x double[5], 3 ints, float
+    assert C.sizeof(nat.XformParams) == 4 + 2 * 32 * 4 + 4 + 8 + 4 + 4 + 2 * 5 * 8 + 3 * 4 + 4
+    assert C.sizeof(nat.CondParams) == 6 * 4
+    # eegspec_cls_eeg_params: (int + pad, 2 x double[13]) twice, int, 2 x int[32], 2 ints, float (+ tail pad to 8)
+    assert C.sizeof(nat.ClsEegParams) == 2 * (8 + 2 * 13 * 8) + 4 + 2 * 32 * 4 + 2 * 4 + 4
+    assert C.sizeof(nat.ClsSpecParams) == 2 * 4 + 8 * 8 + 3 * 4 + 4
+
+
+def test_struct_sizes_match_the_compiled_header(tmp_path):
+    """sizeof of every parameter struct as gcc sees include/eegspec.h == the ctypes mirror."""
+    import subprocess
+
+    src = tmp_path / "sizes.c"
+    src.write_text('#include <stdio.h>\n#include "eegspec.h"\nint main(void){printf("%zu %zu %zu %zu %zu %zu\\n",'
+                   'sizeof(eegspec_stft_plan),sizeof(eegspec_mel_params),sizeof(eegspec_xform_params),'
+                   'sizeof(eegspec_cond_params),sizeof(eegspec_cls_eeg_params),sizeof(eegspec_cls_spec_params));return 0;}\n')
+    exe = tmp_path / "sizes"
+    subprocess.run(["gcc", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)], check=True)
+    got = [int(v) for v in subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.split()]
+    want = [C.sizeof(t) for t in (nat.StftPlan, nat.MelParams, nat.XformParams, nat.CondParams, nat.ClsEegParams,
+                                  nat.ClsSpecParams)]
+    assert got == want
 
 
 @pytest.mark.parametrize("length", [64, 100, 2000, 2001, 10000, 70000, 200000, 720000])
