@@ -17,9 +17,10 @@
 // Row-wise, column-wise and whole-image steps alternate, and one image is 480 KB (more than an SM's shared
 // memory), so the chain is four small HBM-bound kernels with fp32 intermediates:
 //   rowfill   warp per row: nanmean of the row (+ "row is all NaN" status: the reference drops such rows)
-//   columns   CTA = (record, 32 columns): NaN fill, column mean, the notch recurrences forward and backward
-//             (lane = column, double precision), vertical Gaussian -> workspace image
-//   rows      CTA = (record, 8 rows): horizontal Gaussian -> plane 0 of the output (not yet normalised),
+//   columns   thread = (record, column), streaming global memory at full occupancy: NaN fill, column mean, the
+//             notch recurrences forward and backward (double precision), vertical Gaussian in a register window
+//             behind the backward sweep -> workspace image
+//   rows      CTA = (record, 16 rows): horizontal Gaussian -> plane 0 of the output (not yet normalised),
 //             per-CTA min / max
 //   planes    min / max of the record from the partials, normalise plane 0 in place, write planes 1 and 2
 // Algorithmic bytes per record: 4 * 400 * 300 in + 3 * 4 * 400 * 300 out = 1.92 MB; the intermediates add
@@ -32,9 +33,8 @@
 
 namespace eegspec {
 
-constexpr int kSpecColBlock = 32;     // columns per CTA of the column kernel
 constexpr int kSpecPad = 9;           // filtfilt padlen = 3 * max(len(a), len(b))
-constexpr int kSpecRowBlock = 8;      // rows per CTA of the row kernel
+constexpr int kSpecRowBlock = 16;     // rows per CTA of the row kernel
 constexpr int kSpecMaxRadius = 8;
 
 struct SpecArgs {
@@ -78,74 +78,89 @@ __device__ __forceinline__ int reflect_index(int i, int n) {   // scipy.ndimage 
   return i;
 }
 
-__global__ void __launch_bounds__(256) cls_spec_column_kernel(const SpecArgs a) {
-  extern __shared__ __align__(16) float S[];         // [rows + 2 * kSpecPad][kSpecColBlock + 1]
-  constexpr int P = kSpecColBlock + 1;
-  const int tid = threadIdx.x;
-  const int c0 = blockIdx.x * kSpecColBlock;
+// thread = (record, column): everything along axis 0 in one thread, straight out of global memory.  A warp covers
+// 32 consecutive columns, so every row access is one coalesced 128-byte line; 300 K threads per 1 024 records give
+// the latency hiding that a shared-memory slab with one recurrence warp per CTA (the first version: 1.5 ms per
+// 1 024 records) could not.  Pass 1: column mean of the NaN-filled values.  Pass 2: forward notch over the odd
+// extension, output to the workspace image.  Pass 3: backward notch over that (in place, descending rows) with the
+// vertical Gaussian running four rows behind it in a register window.
+template <int RADIUS>
+__global__ void __launch_bounds__(128) cls_spec_column_kernel(const SpecArgs a) {
+  const int c = blockIdx.x * 128 + threadIdx.x;
   const long long rec = blockIdx.y;
-  const int nc = min(kSpecColBlock, a.cols - c0);
-  const float* w = a.win + rec * (long long)a.rows * a.cols;
-  const float* fill = a.rowfill + rec * a.rows;
-  float* X = S + kSpecPad * P;                        // data rows start after the left pad
-  for (int i = tid; i < a.rows * kSpecColBlock; i += 256) {
-    const int r = i / kSpecColBlock, c = i - r * kSpecColBlock;
-    float v = 0.f;
-    if (c < nc) {
-      v = __ldg(w + (long long)r * a.cols + c0 + c);
-      if (v != v) v = fill[r];                        // handle_nan
+  if (c >= a.cols) return;
+  const int n = a.rows;
+  const float* w = a.win + rec * (long long)n * a.cols + c;
+  const float* fill = a.rowfill + rec * n;
+  float* y = a.mid + rec * (long long)n * a.cols + c;        // forward output, then the final column
+  const long long ld = a.cols;
+  auto load = [&](int r) {
+    const float v = __ldg(w + r * ld);
+    return v == v ? v : __ldg(fill + r);                     // handle_nan
+  };
+  double s = 0.0;
+#pragma unroll 8
+  for (int r = 0; r < n; ++r) s += (double)load(r);
+  const double mean = s / (double)n;                         // baseline_correction
+  auto x_at = [&](int r) { return (double)load(r) - mean; };
+  // scipy.signal.filtfilt(method='pad', padtype='odd', padlen=9)
+  const double x_first = x_at(0), x_last = x_at(n - 1);
+  const double b0 = a.nb[0], b1 = a.nb[1], b2 = a.nb[2], a1 = a.na[1], a2 = a.na[2];
+  const double e0 = 2.0 * x_first - x_at(kSpecPad);
+  double z0 = a.zi[0] * e0, z1 = a.zi[1] * e0;
+  auto step = [&](double x) {
+    const double o = fma(b0, x, z0);
+    z0 = fma(b1, x, fma(-a1, o, z1));
+    z1 = fma(b2, x, -a2 * o);
+    return o;
+  };
+  for (int e = 0; e < kSpecPad; ++e) step(2.0 * x_first - x_at(kSpecPad - e));     // left extension: outputs not needed
+#pragma unroll 4
+  for (int r = 0; r < n; ++r) y[r * ld] = (float)step(x_at(r));
+  double tail[kSpecPad];                                     // forward outputs over the right extension
+#pragma unroll
+  for (int k = 0; k < kSpecPad; ++k) tail[k] = step(2.0 * x_last - x_at(n - 2 - k));
+  // backward pass: starts at the end of the extension with zi * (last forward output)
+  z0 = a.zi[0] * tail[kSpecPad - 1];
+  z1 = a.zi[1] * tail[kSpecPad - 1];
+#pragma unroll
+  for (int k = kSpecPad - 1; k >= 0; --k) step(tail[k]);
+  // Rows n - 1 .. 0 come out of the backward recurrence one per step; W[k] = f[r + k] (k = 0 .. 2 RADIUS) is the
+  // register window behind it and the Gaussian of row r + RADIUS is complete once f[r] is known.  Reflection
+  // (scipy.ndimage 'reflect'): below the last row f[n - 1 + j] = f[n - j] is filled in when row n - 1 is emitted
+  // and then simply shifts along; above the first row the recurrence has ended and f[-j] = f[j - 1] is taken
+  // from the window itself (index 2 j - 1 after the shift).
+  float W[2 * RADIUS + 1];
+#pragma unroll
+  for (int k = 0; k <= 2 * RADIUS; ++k) W[k] = 0.f;
+  for (int r = n - 1; r >= -RADIUS; --r) {
+    float f = 0.f;
+    if (r >= 0) f = (float)step((double)y[r * ld]);
+#pragma unroll
+    for (int k = 2 * RADIUS; k > 0; --k) W[k] = W[k - 1];
+    if (r < 0) {
+#pragma unroll
+      for (int k = 1; k <= 2 * RADIUS; k += 2)
+        if (k == -2 * r - 1) f = W[k];
     }
-    X[r * P + c] = v;
-  }
-  __syncthreads();
-  if (tid < kSpecColBlock && tid < nc) {
-    const int c = tid, n = a.rows;
-    double s = 0.0;
-    for (int r = 0; r < n; ++r) s += (double)X[r * P + c];
-    const double mean = s / (double)n;                // baseline_correction
-    auto x_at = [&](int r) { return (double)X[r * P + c] - mean; };
-    // scipy.signal.filtfilt(method='pad', padtype='odd', padlen=9): odd extension, forward, backward.
-    // The forward output replaces the slab in place (S row e = extended sample e; data sample r sits in S row
-    // r + 9).  Left extension: reads data rows 9 .. 1 (S rows 18 .. 10) while writing S rows 0 .. 8.  Main part:
-    // reads and then writes the same row.  Right extension: needs data rows n - 2 .. n - 10, whose S rows the main
-    // part has already overwritten -- so those nine values are taken into registers first.
-    const double x_first = x_at(0), x_last = x_at(n - 1);
-    double tail[kSpecPad];
+    W[0] = f;
+    const int rc = r + RADIUS;               // centre of the window: W[RADIUS] = f[rc]
+    if (rc <= n - 1) {
+      if (rc == n - 1) {
 #pragma unroll
-    for (int k = 0; k < kSpecPad; ++k) tail[k] = x_at(n - 2 - k);
-    const double b0 = a.nb[0], b1 = a.nb[1], b2 = a.nb[2], a1 = a.na[1], a2 = a.na[2];
-    const int ne = n + 2 * kSpecPad;
-    float* Y = S;
-    const double e0 = 2.0 * x_first - x_at(kSpecPad);
-    double z0 = a.zi[0] * e0, z1 = a.zi[1] * e0;
-    auto step = [&](double x) {
-      const double y = fma(b0, x, z0);
-      z0 = fma(b1, x, fma(-a1, y, z1));
-      z1 = fma(b2, x, -a2 * y);
-      return y;
-    };
-    for (int e = 0; e < kSpecPad; ++e) Y[e * P + c] = (float)step(2.0 * x_first - x_at(kSpecPad - e));
-    for (int r = 0; r < n; ++r) Y[(r + kSpecPad) * P + c] = (float)step(x_at(r));
+        for (int k = 1; k <= RADIUS; ++k) W[RADIUS + k] = W[RADIUS - k + 1];
+      }
+      float acc = a.g[0] * W[RADIUS];
 #pragma unroll
-    for (int k = 0; k < kSpecPad; ++k) Y[(n + kSpecPad + k) * P + c] = (float)step(2.0 * x_last - tail[k]);
-    const double y_last = (double)Y[(ne - 1) * P + c];
-    z0 = a.zi[0] * y_last;
-    z1 = a.zi[1] * y_last;
-    for (int e = ne - 1; e >= 0; --e) Y[e * P + c] = (float)step((double)Y[e * P + c]);
-  }
-  __syncthreads();
-  // vertical Gaussian (axis 0), reflect at the image's first / last row; the filtered image is S rows 9 .. 9 + rows
-  float* o = a.mid + rec * (long long)a.rows * a.cols;
-  for (int i = tid; i < a.rows * kSpecColBlock; i += 256) {
-    const int r = i / kSpecColBlock, c = i - r * kSpecColBlock;
-    if (c >= nc) continue;
-    float acc = a.g[0] * X[r * P + c];
-    for (int k = 1; k <= a.radius; ++k)
-      acc += a.g[k] * (X[reflect_index(r - k, a.rows) * P + c] + X[reflect_index(r + k, a.rows) * P + c]);
-    o[(long long)r * a.cols + c0 + c] = acc;
+      for (int k = 1; k <= RADIUS; ++k) acc += a.g[k] * (W[RADIUS - k] + W[RADIUS + k]);
+      y[rc * ld] = acc;                      // row rc was consumed RADIUS steps ago: never read again
+    }
   }
 }
 
+// CTA = (record, kSpecRowBlock rows); thread = column (and column + 256 ...), looping over the rows: no divisions,
+// reflected neighbour columns resolved once per thread.
+template <int RADIUS>
 __global__ void __launch_bounds__(256) cls_spec_row_kernel(const SpecArgs a) {
   extern __shared__ __align__(16) float R[];         // [kSpecRowBlock][cols]
   __shared__ float red_lo[8], red_hi[8];
@@ -154,19 +169,28 @@ __global__ void __launch_bounds__(256) cls_spec_row_kernel(const SpecArgs a) {
   const long long rec = blockIdx.y;
   const int nr = min(kSpecRowBlock, a.rows - r0);
   const float* m = a.mid + (rec * a.rows + r0) * (long long)a.cols;
-  for (int i = tid; i < nr * a.cols; i += 256) R[i] = m[i];
+  const int n_el = nr * a.cols;
+  if (!(a.cols & 3)) {
+    for (int i = tid; i < (n_el >> 2); i += 256) reinterpret_cast<float4*>(R)[i] = reinterpret_cast<const float4*>(m)[i];
+  } else {
+    for (int i = tid; i < n_el; i += 256) R[i] = m[i];
+  }
   __syncthreads();
   float lo = INFINITY, hi = -INFINITY;
   float* o = a.out + (rec * 3 * a.rows + r0) * (long long)a.cols;   // plane 0
-  for (int i = tid; i < nr * a.cols; i += 256) {
-    const int r = i / a.cols, c = i - r * a.cols;
-    const float* row = R + r * a.cols;
-    float acc = a.g[0] * row[c];
-    for (int k = 1; k <= a.radius; ++k)
-      acc += a.g[k] * (row[reflect_index(c - k, a.cols)] + row[reflect_index(c + k, a.cols)]);
-    o[i] = acc;
-    lo = fminf(lo, acc);
-    hi = fmaxf(hi, acc);
+  for (int c = tid; c < a.cols; c += 256) {
+    int nb_l[RADIUS], nb_r[RADIUS];
+#pragma unroll
+    for (int k = 1; k <= RADIUS; ++k) { nb_l[k - 1] = reflect_index(c - k, a.cols); nb_r[k - 1] = reflect_index(c + k, a.cols); }
+    for (int r = 0; r < nr; ++r) {
+      const float* row = R + r * a.cols;
+      float acc = a.g[0] * row[c];
+#pragma unroll
+      for (int k = 1; k <= RADIUS; ++k) acc += a.g[k] * (row[nb_l[k - 1]] + row[nb_r[k - 1]]);
+      o[r * a.cols + c] = acc;
+      lo = fminf(lo, acc);
+      hi = fmaxf(hi, acc);
+    }
   }
 #pragma unroll
   for (int s = 16; s > 0; s >>= 1) {
@@ -275,18 +299,13 @@ int cls_spec_launch(const float* win, long long batch, const eegspec_cls_spec_pa
   cls_spec_rowfill_kernel<<<dim3((unsigned)((p->rows + 7) / 8), (unsigned)batch), 256, 0, st>>>(a);
   count_launch();
   if ((e = cudaGetLastError()) != cudaSuccess) return (int)e;
-  const size_t smem_c = sizeof(float) * (size_t)(p->rows + 2 * kSpecPad) * (kSpecColBlock + 1);
-  if (smem_c > 200 * 1024) return EEGSPEC_EUNSUPPORTED;
-  if (smem_c > 48 * 1024) {
-    e = cudaFuncSetAttribute(cls_spec_column_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_c);
-    if (e != cudaSuccess) return (int)e;
-  }
-  cls_spec_column_kernel<<<dim3((unsigned)((p->cols + kSpecColBlock - 1) / kSpecColBlock), (unsigned)batch), 256, smem_c, st>>>(a);
+  if (radius != 4) return EEGSPEC_EUNSUPPORTED;   // sigma 1, truncate 4: the reference's (the kernels unroll the 9 taps)
+  cls_spec_column_kernel<4><<<dim3((unsigned)((p->cols + 127) / 128), (unsigned)batch), 128, 0, st>>>(a);
   count_launch();
   if ((e = cudaGetLastError()) != cudaSuccess) return (int)e;
   const size_t smem_r = sizeof(float) * (size_t)kSpecRowBlock * p->cols;
   if (smem_r > 48 * 1024) return EEGSPEC_EUNSUPPORTED;
-  cls_spec_row_kernel<<<dim3((unsigned)a.n_row_blocks, (unsigned)batch), 256, smem_r, st>>>(a);
+  cls_spec_row_kernel<4><<<dim3((unsigned)a.n_row_blocks, (unsigned)batch), 256, smem_r, st>>>(a);
   count_launch();
   if ((e = cudaGetLastError()) != cudaSuccess) return (int)e;
   cls_spec_planes_kernel<<<dim3(8, (unsigned)batch), 256, 0, st>>>(a);

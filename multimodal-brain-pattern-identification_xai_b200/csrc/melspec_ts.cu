@@ -148,6 +148,32 @@ __device__ __forceinline__ void t_st_async_peer(uint32_t raddr, uint32_t rbar, f
                : "memory");
 }
 
+// L2 residency hints.  The stash (finished chains parked in the record's own output rows) is re-read one record
+// later by the transposition; without hints the 819 MB input stream evicts part of it first (round 1: 1.87 GB of
+// DRAM traffic per 1 024 records against 1.36 GB algorithmic).  Electrode rows are read with evict_first (each
+// is used by at most four pairs within a few tiles), stash stores ask for evict_last, final pixels evict_first.
+__device__ __forceinline__ uint64_t t_policy_evict_first() {
+  uint64_t p;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+  return p;
+}
+__device__ __forceinline__ uint64_t t_policy_evict_last() {
+  uint64_t p;
+  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
+  return p;
+}
+__device__ __forceinline__ void t_st_f4_hint(float* ptr, float4 v, uint64_t pol) {
+  asm volatile("st.global.L2::cache_hint.v4.f32 [%0], {%1, %2, %3, %4}, %5;" ::"l"(ptr), "f"(v.x), "f"(v.y), "f"(v.z),
+               "f"(v.w), "l"(pol)
+               : "memory");
+}
+__device__ __forceinline__ void t_bulk_g2s_hint(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar, uint64_t pol) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::"r"(dst),
+      "l"(src), "r"(bytes), "r"(bar), "l"(pol)
+      : "memory");
+}
+
 // Wait with an explicit back-off.  c_mbar_wait compiles to TRYWAIT / NANOSLEEP.SYNCS / PHASECHK / BRA and
 // a waiting warp goes round that loop every ~20 ns: sixteen epilogue warps in the exchange wait and eight
 // build warps waiting for a ring slot executed 40 % of the kernel's warp instructions there.
@@ -352,6 +378,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTThreads, 1) melspe
       // ---- TMA prefetch: both electrode rows of pair j + 1 once the difference of pair j has
       //      consumed the staging buffers
       if (lane == 0) {
+        const uint64_t pol_stream = t_policy_evict_first();
         auto issue_load = [&](int j) {
           int rec;
           const int pr = pair_of(j, rec);
@@ -361,8 +388,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTThreads, 1) melspe
           const uint32_t load_bar = load_bar0 + 8 * (j & 1);
           float* st = stage + (j & 1) * 2 * kCStageFloats;
           c_mbar_expect_tx(load_bar, 2 * bytes);
-          c_bulk_g2s(c_smem_u32(st), base + a.pair_a[pr] * a.ch_stride, bytes, load_bar);
-          c_bulk_g2s(c_smem_u32(st + kCStageFloats), base + a.pair_b[pr] * a.ch_stride, bytes, load_bar);
+          t_bulk_g2s_hint(c_smem_u32(st), base + a.pair_a[pr] * a.ch_stride, bytes, load_bar, pol_stream);
+          t_bulk_g2s_hint(c_smem_u32(st + kCStageFloats), base + a.pair_b[pr] * a.ch_stride, bytes, load_bar, pol_stream);
         };
         // Stagger the clusters by a quarter of a chain each: all CTAs do identical work and would
         // otherwise store their finished chains in the same instant (L2 write bursts).
@@ -555,6 +582,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTThreads, 1) melspe
     static_assert(MELGEN_COL0_P4_2 == 2 * MELGEN_COL0_P4_1 && MELGEN_COL0_P4_3 == 3 * MELGEN_COL0_P4_1, "part pitch");
     auto park_col = [](int g) { return (uint32_t)(8 * (1 + g / 2) + (g & 1) * kTBins); };
     const uint32_t lane_base = tmem_base + ((uint32_t)(32 * (warp & 3)) << 16);
+    const uint64_t pol_keep = t_policy_evict_last(), pol_done = t_policy_evict_first();
     const uint32_t peer_pv0 = t_mapa(c_smem_u32(&sh.pv[0][warp]), (uint32_t)peer), peer_xch0 = t_mapa(xch_bar0, (uint32_t)peer);
     float acc[kTMels];
 #pragma unroll
@@ -613,7 +641,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTThreads, 1) melspe
         v.y = fmaf(a.out_gain, acc[4 * g + 1] - csum, a.out_bias);
         v.z = fmaf(a.out_gain, acc[4 * g + 2] - csum, a.out_bias);
         v.w = fmaf(a.out_gain, acc[4 * g + 3] - csum, a.out_bias);
-        *reinterpret_cast<float4*>(o + 4 * g * mstride) = v;
+        t_st_f4_hint(o + 4 * g * mstride, v, pol_keep);
       }
     };
     // A finished record is turned into the final [frame][chain] pixels one group of four mel
@@ -631,10 +659,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTThreads, 1) melspe
       float* r = row_seg(rec) + 4 * g * mstride + 4 * t_frame;
       // no barrier: the four slots read and the four slots written are this thread's own (chain_done
       // and this function address rows 4 g .. 4 g + 3 at the same 16 bytes, 4 t_frame)
-      *reinterpret_cast<float4*>(r + 0 * mstride) = make_float4(tv[0].x, tv[1].x, tv[2].x, tv[3].x);
-      *reinterpret_cast<float4*>(r + 1 * mstride) = make_float4(tv[0].y, tv[1].y, tv[2].y, tv[3].y);
-      *reinterpret_cast<float4*>(r + 2 * mstride) = make_float4(tv[0].z, tv[1].z, tv[2].z, tv[3].z);
-      *reinterpret_cast<float4*>(r + 3 * mstride) = make_float4(tv[0].w, tv[1].w, tv[2].w, tv[3].w);
+      t_st_f4_hint(r + 0 * mstride, make_float4(tv[0].x, tv[1].x, tv[2].x, tv[3].x), pol_done);
+      t_st_f4_hint(r + 1 * mstride, make_float4(tv[0].y, tv[1].y, tv[2].y, tv[3].y), pol_done);
+      t_st_f4_hint(r + 2 * mstride, make_float4(tv[0].z, tv[1].z, tv[2].z, tv[3].z), pol_done);
+      t_st_f4_hint(r + 3 * mstride, make_float4(tv[0].w, tv[1].w, tv[2].w, tv[3].w), pol_done);
     };
 
     // Per tile: main (power, mel, lg2, park) -> contribute the maximum -> wait for the exchange

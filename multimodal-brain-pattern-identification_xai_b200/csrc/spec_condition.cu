@@ -26,8 +26,8 @@
 
 namespace eegspec {
 
-constexpr int kCondJ = 64;          // output samples per CTA
-constexpr int kCondThreads = 256;   // 64 samples x 4 output-channel groups
+constexpr int kCondJ = 128;         // output samples per CTA
+constexpr int kCondThreads = 256;
 constexpr int kCondKw = 3, kCondKh = 3, kCondStrideT = 8, kCondPadT = 2, kCondPadF = 1;
 
 struct CondArgs {
@@ -46,10 +46,12 @@ struct CondArgs {
 __global__ void __launch_bounds__(kCondThreads) spec_condition_kernel(const CondArgs a) {
   extern __shared__ __align__(16) float sm[];
   const int K = a.n_ch * kCondKh;
-  float* A = sm;                                        // [2][kCondJ][k_pad]   gathered image values per position
+  float* A = sm;                                        // [2 kCondJ][k_pad]    gathered image values per position
   float* W = A + 2 * kCondJ * a.k_pad;                  // [3][K][h2]           w[c][h][kf][kt] -> W[kt][c * 3 + kf][h]
-  float* lam = W + kCondKw * K * a.h2;                  // [kCondJ]
-  int* kts = reinterpret_cast<int*>(lam + kCondJ);      // [2][kCondJ]          kernel column of the position, -1 = bias only
+  __shared__ float lam[kCondJ];
+  __shared__ int kts[2 * kCondJ];                       // kernel column of position p = which * kCondJ + jj, -1 = bias only
+  __shared__ int fs[2 * kCondJ], tqs[2 * kCondJ];
+  __shared__ int live[2 * kCondJ], n_live;              // positions that read the image (3 / 8 of them)
 
   const int tid = threadIdx.x;
   const int tiles = (a.out_len + kCondJ - 1) / kCondJ;
@@ -60,15 +62,16 @@ __global__ void __launch_bounds__(kCondThreads) spec_condition_kernel(const Cond
   const float* sb = a.partner ? a.spec + (long long)a.partner[rec] * img : nullptr;
   const bool mix = sb != nullptr && sb != sa;
 
+  if (tid == 0) n_live = 0;
   for (int i = tid; i < kCondKw * K * a.h2; i += kCondThreads) {
     const int h = i % a.h2, k = (i / a.h2) % K, kt = i / (a.h2 * K);
     const int c = k / kCondKh, kf = k - c * kCondKh;
     W[i] = __ldg(a.weight + (((long long)c * a.h2 + h) * kCondKh + kf) * kCondKw + kt);
   }
+  __syncthreads();
   // ---- positions of this CTA's samples (ATen's linear / align_corners=False arithmetic in fp32)
-  __shared__ int fs[2][kCondJ], tqs[2][kCondJ];
-  if (tid < 2 * kCondJ) {
-    const int jj = tid & (kCondJ - 1), which = tid >> 6;
+  {
+    const int jj = tid & (kCondJ - 1), which = tid >> 7;          // 256 threads = 2 x kCondJ positions
     const int j = j0 + jj;
     float src = __fsub_rn(__fmul_rn(a.scale, (float)j + 0.5f), 0.5f);
     src = src < 0.f ? 0.f : src;
@@ -79,37 +82,50 @@ __global__ void __launch_bounds__(kCondThreads) spec_condition_kernel(const Cond
     const int f = i / a.t_out, t = i - f * a.t_out;
     const int kt = (t + kCondPadT) % kCondStrideT;
     const int tq = (t + kCondPadT) / kCondStrideT;
-    const bool live = j < a.out_len && kt < kCondKw && tq < a.n_cols;
-    kts[which * kCondJ + jj] = live ? kt : -1;
-    fs[which][jj] = f;
-    tqs[which][jj] = tq;
+    const bool is_live = j < a.out_len && kt < kCondKw && tq < a.n_cols;
+    kts[tid] = is_live ? kt : -1;
+    fs[tid] = f;
+    tqs[tid] = tq;
+    if (is_live) live[atomicAdd(&n_live, 1)] = tid;
   }
   __syncthreads();
-  // ---- gather: A[which][jj][c * 3 + kf] = in[c, f + 1 - kf, t'] (0 outside the image)
-  for (int i = tid; i < 2 * kCondJ * K; i += kCondThreads) {
-    const int p = i / K, k = i - p * K;               // consecutive threads: consecutive k of one position
-    const int which = p >> 6, jj = p & (kCondJ - 1);
-    if (kts[which * kCondJ + jj] < 0) continue;
-    const int c = k / kCondKh, kf = k - c * kCondKh;
-    const int f = fs[which][jj] + kCondPadF - kf;
-    float v = 0.f;
-    if (f >= 0 && f < a.n_freqs) {
-      const long long off = ((long long)c * a.n_freqs + f) * a.n_cols + tqs[which][jj];
-      v = __ldg(sa + off);
-      if (mix) v = a.alpha * v + (1.f - a.alpha) * __ldg(sb + off);     // diffEEG.py:143
+  // ---- gather: A[p][c * 3 + kf] = in[c, f + 1 - kf, t'] (0 outside the image).  A thread owns ONE k (its channel /
+  // kernel-row offset is computed once) and walks the live positions four apart: the loads of the unrolled
+  // iterations are independent and in flight together.
+  {
+    const int k = tid & 63, lane_p = tid >> 6;                    // 64 k slots (K <= 64 served per pass) x 4 position lanes
+    const int nl = n_live;
+    for (int k0 = 0; k0 < K; k0 += 64) {
+      const int kk = k0 + k;
+      if (kk < K) {
+        const int c = kk / kCondKh, kf = kk - c * kCondKh;
+        const long long ch_off = (long long)c * a.n_freqs * a.n_cols;
+        const int df = kCondPadF - kf;
+#pragma unroll 4
+        for (int u = lane_p; u < nl; u += 4) {
+          const int p = live[u];
+          const int f = fs[p] + df;
+          float v = 0.f;
+          if (f >= 0 && f < a.n_freqs) {
+            const long long off = ch_off + (long long)f * a.n_cols + tqs[p];
+            v = __ldg(sa + off);
+            if (mix) v = a.alpha * v + (1.f - a.alpha) * __ldg(sb + off);     // diffEEG.py:143
+          }
+          A[p * a.k_pad + kk] = v;
+        }
+      }
     }
-    A[(which * kCondJ + jj) * a.k_pad + k] = v;
   }
   __syncthreads();
-  // ---- contraction + relu + interpolation: thread = (sample jj, output channels hg, hg + 4, ...), 4 at a time
-  const int jj = tid & (kCondJ - 1), hg = tid >> 6;
+  // ---- contraction + relu + interpolation: thread = (sample jj, output channels hg, hg + 2, ...), 4 at a time
+  const int jj = tid & (kCondJ - 1), hg = tid >> 7;
   const int j = j0 + jj;
   if (j >= a.out_len) return;
   const int kt0 = kts[jj], kt1 = kts[kCondJ + jj];
   const float l1 = lam[jj], l0 = 1.f - l1;
   const float* A0 = A + jj * a.k_pad;
   const float* A1 = A + (kCondJ + jj) * a.k_pad;
-  for (int h0 = 4 * hg; h0 < a.h2; h0 += 16) {
+  for (int h0 = 4 * hg; h0 < a.h2; h0 += 8) {
     float v0[4], v1[4];
 #pragma unroll
     for (int i = 0; i < 4; ++i) v0[i] = v1[i] = (h0 + i < a.h2) ? __ldg(a.bias + h0 + i) : 0.f;
@@ -164,8 +180,7 @@ int spec_condition_launch(const float* spec, long long batch, const eegspec_cond
   a.scale = (float)a.in_len / (float)a.out_len;   // ATen: area_pixel_compute_scale<float>
   a.alpha = p->mix_alpha;
   const int K = a.n_ch * kCondKh;
-  const size_t smem = sizeof(float) * ((size_t)2 * kCondJ * a.k_pad + (size_t)kCondKw * K * a.h2 + kCondJ) +
-                      sizeof(int) * 2 * kCondJ;
+  const size_t smem = sizeof(float) * ((size_t)2 * kCondJ * a.k_pad + (size_t)kCondKw * K * a.h2);
   if (smem > 200 * 1024) return EEGSPEC_EUNSUPPORTED;
   if (smem > 48 * 1024) {
     const cudaError_t e = cudaFuncSetAttribute(spec_condition_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

@@ -1,0 +1,27 @@
+"""Timing of the rows (f)2-(f)4 kernels alone (run on the GPU box)."""
+import sys; sys.path.insert(0, ".")
+import torch, b200spec
+g = torch.Generator(device="cuda").manual_seed(1)
+def timed(fn, n=10):
+    for _ in range(3): fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(n): fn()
+    e1.record(); torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / n
+which = sys.argv[1:] or ["f2", "f3", "f4"]
+if "f3" in which:
+    win = torch.rand((1024, 400, 300), device="cuda", generator=g) * 40
+    print("f3 ms/1024:", timed(lambda: b200spec.process_spectrogram(win, check=False)))
+    del win
+if "f2" in which:
+    img = torch.rand((1024, 19, 33, 2000), device="cuda", generator=g)
+    w = torch.randn((19, 16, 3, 3), device="cuda") * 0.1; b = torch.zeros(16, device="cuda")
+    print("f2 ms/1024:", timed(lambda: b200spec.spectrogram_condition(img, w, b, 2000)))
+    del img
+if "f4" in which:
+    for B in (1024, 4096):
+        x = torch.randn((B, 10000, 20), device="cuda", generator=g).cumsum_(1)
+        print(f"f4 ms/{B}:", timed(lambda: b200spec.process_eeg(x, check=False), 4))
+        del x
