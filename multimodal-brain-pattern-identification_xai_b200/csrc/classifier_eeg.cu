@@ -98,7 +98,7 @@ __device__ __forceinline__ double pw_combine(const double (&r)[8]) {
 }
 
 template <int N1, int N2, bool SKIP>
-__global__ void __launch_bounds__(32) classifier_eeg_filter_kernel(const ClsFilterArgs a) {
+__global__ void __launch_bounds__(32) classifier_eeg_filter_kernel(const __grid_constant__ ClsFilterArgs a) {
   const int lane = threadIdx.x;
   const long long rec = blockIdx.x;
   const long long n = a.n;
