@@ -694,6 +694,11 @@ def leg_eeg_transform(torch, b200spec, timed, keep, peak, world, args):
     return out
 
 
+class DiffEegCfg:
+    """The diffEEG_trainer keys compute_stft reads (configs/config.yaml)."""
+    diffEEG_trainer = {"stft_n_fft": 64, "stft_hop_length": 32, "stft_window": "hann"}
+
+
 def leg_next_rows(torch, b200spec, timed, keep, peak, world, args):
     """Rows (f)2-(f)4: the consumer front end of DiffEEG and the classifier-side preprocessing."""
     out = {}
@@ -725,6 +730,32 @@ def leg_next_rows(torch, b200spec, timed, keep, peak, world, args):
                                         "sectors (2.7 MB) + 128 KB out per record",
                                         image_GBps_if_read_whole=batch * 4 * 19 * 33 * 2000 / (ms * 1e-3 / steps) / 1e9)}
         del img, flush
+
+        # the same condition straight from the (B,19,2000) rows: compute_stft's kernel hands over its normalised knots
+        # (33 x 64 {value, delta} per row) and the gather evaluates the 0.76 % of the image it needs from them
+        x = torch.randn((batch, 19, 2000), device="cuda", generator=gen)
+        flush = torch.zeros(256 << 20 >> 2, device="cuda") if batch == 64 else None
+
+        def step_k():
+            keep["c"] = b200spec.stft_condition(x, DiffEegCfg, w, b, 2000)
+
+        def step_2():
+            keep["c"] = b200spec.spectrogram_condition(b200spec.compute_stft(x, DiffEegCfg), w, b, 2000)
+
+        ms_k, _ = timed(step_k, steps, 3, flush=flush)
+        ms_2, _ = timed(step_2, steps, 3, flush=flush)
+        keep.pop("c", None)
+        bytes_k = 4 * 19 * 2000 + 4 * 16 * 2000
+        f2[key + "_from_rows"] = {
+            "what": "b200spec.stft_condition = eegspec_stft_knots_f32 + eegspec_spec_condition_knots_f32: compute_stft and the "
+                    "condition without the (B,19,33,2000) image in between; bit-identical to the two-call path",
+            "workload": f"({batch},19,2000) rows -> ({batch},16,2000)",
+            "value": world * batch * steps / (ms_k * 1e-3), "unit": UNIT, "ms_per_step": ms_k / steps,
+            "two_call_ms_per_step": ms_2 / steps,
+            "roofline": roofline(batch * bytes_k, ms_k * 1e-3 / steps, peak,
+                                 f"stft_image_kernel (knots only) + spec_condition_kernel, {bytes_k} B/record algorithmic "
+                                 "(rows in, condition out); the 321 KB of knots per record in between stay mostly in L2")}
+        del x, flush
     out["f2_diffeeg_condition"] = f2
 
     # ---- (f)4: classifier-side EEG preprocessing

@@ -250,6 +250,20 @@ int eegspec_spec_condition_f32(const float *spec, int64_t batch, const eegspec_c
                                const float *weight, const float *bias, const int32_t *partner,
                                float *out, void *stream);
 
+/* The same operator WITHOUT the image: compute_stft's kernel stops after its normalisation and hands over the
+ * F x n_frames knot pairs {value, delta} every pixel of the image is a linear function of
+ * (pixel = sat(value + delta * fraction), DiffEEG_utils.py:57-61, 72-74); the condition kernel evaluates the
+ * 85 500 pixels it needs from them.  Per record of the DiffEEG batch: 152 KB of signal in, 321 KB of knots through
+ * L2, 128 KB out -- instead of writing a 5 MB image and gathering 2.7 MB of it back.  Bit-identical to
+ * eegspec_spec_condition_f32(eegspec_stft_image_f32(x)).
+ *   knots: device, (rows, nperseg/2+1, n_frames) pairs of fp32, 8-byte aligned, n_frames from eegspec_stft_plan_make.
+ *   EEGSPEC_EUNSUPPORTED when a row's knots do not fit shared memory or the plan decimates (very long rows). */
+int eegspec_stft_knots_f32(const float *x, int64_t rows, int64_t length, int64_t row_stride, int nperseg,
+                           int noverlap, int64_t out_cols, float eps, float *knots, void *stream);
+int eegspec_spec_condition_knots_f32(const float *knots, int32_t n_frames, int64_t batch,
+                                     const eegspec_cond_params *p, const float *weight, const float *bias,
+                                     const int32_t *partner, float *out, void *stream);
+
 /* ------------------------------------------------------------------------------------------
  * Rows (f)4 / (f)3 -- the classifier-side preprocessing of the multimodal model's two inputs
  *   (CombinedDataset, /root/reference/root/jupyter_notebooks/XAI_Multimodality.py:1114-1307; the helpers

@@ -31,6 +31,7 @@ _API = {
     "install": "transform",
     "launch_count": "transform",
     "spectrogram_condition": "diffeeg",
+    "stft_condition": "diffeeg",
     "process_eeg": "classifier",
     "process_spectrogram": "classifier",
     "spectrogram_window": "classifier",

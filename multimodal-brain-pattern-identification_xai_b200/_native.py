@@ -119,6 +119,10 @@ SIGNATURES = {
     "eegspec_classifier_spec_workspace": (C.c_size_t, [C.c_int64, C.POINTER(ClsSpecParams)]),
     "eegspec_classifier_spec_f32": (C.c_int, [C.c_void_p, C.c_int64, C.POINTER(ClsSpecParams), C.c_void_p, C.c_void_p,
                                               C.c_void_p, C.c_size_t, C.c_void_p]),
+    "eegspec_stft_knots_f32": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_int, C.c_int, C.c_int64,
+                                         C.c_float, C.c_void_p, C.c_void_p]),
+    "eegspec_spec_condition_knots_f32": (C.c_int, [C.c_void_p, C.c_int32, C.c_int64, C.POINTER(CondParams), C.c_void_p,
+                                                   C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "eegspec_launch_count": (C.c_int64, []),
 }
 

@@ -433,6 +433,19 @@ int eegspec_classifier_spec_f32(const float* win, int64_t batch, const eegspec_c
   return cls_spec_launch(win, batch, p, out, status, workspace, workspace_bytes, static_cast<cudaStream_t>(stream));
 }
 
+int eegspec_stft_knots_f32(const float* x, int64_t rows, int64_t length, int64_t row_stride, int nperseg, int noverlap,
+                           int64_t out_cols, float eps, float* knots, void* stream) {
+  return stft_knots_launch(x, rows, length, row_stride, nperseg, noverlap, out_cols, eps, knots,
+                           static_cast<cudaStream_t>(stream));
+}
+
+int eegspec_spec_condition_knots_f32(const float* knots, int32_t n_frames, int64_t batch, const eegspec_cond_params* p,
+                                     const float* weight, const float* bias, const int32_t* partner, float* out,
+                                     void* stream) {
+  return spec_condition_knots_launch(knots, n_frames, batch, p, weight, bias, partner, out,
+                                     static_cast<cudaStream_t>(stream));
+}
+
 int64_t eegspec_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 
 }  // extern "C"

@@ -19,6 +19,8 @@ size_t stft_image_workspace(long long rows, long long length, int nperseg, int n
 int stft_image_launch(const float* x, long long rows, long long length, long long row_stride,
                       int nperseg, int noverlap, long long out_cols, float eps, float* out,
                       void* workspace, size_t workspace_bytes, cudaStream_t st);
+int stft_knots_launch(const float* x, long long rows, long long length, long long row_stride, int nperseg,
+                      int noverlap, long long out_cols, float eps, float* knots, cudaStream_t st);
 int stft_logmag_launch(const float* x, long long rows, long long length, long long row_stride,
                        int nperseg, int noverlap, float* out, cudaStream_t st);
 
@@ -54,6 +56,9 @@ void cls_spec_params_default(eegspec_cls_spec_params* p);
 size_t cls_spec_workspace(long long batch, const eegspec_cls_spec_params* p);
 int cls_spec_launch(const float* win, long long batch, const eegspec_cls_spec_params* p, float* out, int* status,
                     void* workspace, size_t workspace_bytes, cudaStream_t st);
+
+int spec_condition_knots_launch(const float* knots, int n_frames, long long batch, const eegspec_cond_params* p,
+                                const float* weight, const float* bias, const int* partner, float* out, cudaStream_t st);
 
 // eegtransform.cu
 void xform_params_default(eegspec_xform_params* p);

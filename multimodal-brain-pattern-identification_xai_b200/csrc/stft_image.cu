@@ -34,6 +34,7 @@ struct StftArgs {
   int out_cols, D, r_step, r32_step, small_index, ends_only, n_items;
   float inv_d, eps;
   int stage;   // thread-per-frame path: row staged in shared memory (aliases the knot array)
+  int knots_only;   // stop after phase 2 and write the normalised knots {value, delta} instead of the image
 };
 
 // Left knot and remainder of output column j:  j*(n-1) = i*D + rem, clamped to the last segment.
@@ -497,6 +498,23 @@ stft_image_kernel(const StftArgs a) {
   }
   __syncthreads();
 
+  if constexpr (MODE == 0) {
+    if (a.knots_only) {
+      // The image is a pure function of these F x n_frames knot pairs (pixel = sat(value + delta * fraction)): a
+      // consumer that only samples the image (row (f)2, spec_condition.cu) reads 17 KB per row instead of 264 KB.
+      // Rows poisoned by a NaN sample are marked {NaN, 0}.
+      float2* ko = reinterpret_cast<float2*>(a.out) + row * (long long)F * a.n_frames;
+      const float2* S2 = reinterpret_cast<const float2*>(S);
+      const int nf = (int)a.n_frames;
+      for (int f = warp; f < F; f += nwarps) {
+        const bool bad = rowflag[f] != 0;
+        for (int s = lane; s < nf; s += 32)
+          ko[f * nf + s] = bad ? make_float2(__int_as_float(0x7fc00000), 0.f) : S2[(long long)f * a.n_pad + s];
+      }
+      return;
+    }
+  }
+
   // Phase 3: image write.  A thread keeps the four brackets of its column quad in registers
   // and walks the frequency rows; a warp emits one contiguous 512 B line per row.
   const int Q = a.out_cols >> 2;
@@ -690,9 +708,27 @@ static int dispatch(int nperseg, const StftArgs& a, long long grid, size_t smem,
   }
 }
 
+static int stft_launch_common(const float* x, long long rows, long long length, long long row_stride, int nperseg,
+                              int noverlap, long long out_cols, float eps, float* out, void* workspace,
+                              size_t workspace_bytes, bool knots_only, cudaStream_t st);
+
 int stft_image_launch(const float* x, long long rows, long long length, long long row_stride,
                       int nperseg, int noverlap, long long out_cols, float eps, float* out,
                       void* workspace, size_t workspace_bytes, cudaStream_t st) {
+  return stft_launch_common(x, rows, length, row_stride, nperseg, noverlap, out_cols, eps, out, workspace,
+                            workspace_bytes, false, st);
+}
+
+// knots: (rows, nperseg/2+1, n_frames) float2 {normalised value, normalised delta to the next knot}.  Served when the
+// knot array of a row fits shared memory and every frame is a knot (no decimating plan); EUNSUPPORTED otherwise.
+int stft_knots_launch(const float* x, long long rows, long long length, long long row_stride, int nperseg,
+                      int noverlap, long long out_cols, float eps, float* knots, cudaStream_t st) {
+  return stft_launch_common(x, rows, length, row_stride, nperseg, noverlap, out_cols, eps, knots, nullptr, 0, true, st);
+}
+
+static int stft_launch_common(const float* x, long long rows, long long length, long long row_stride, int nperseg,
+                              int noverlap, long long out_cols, float eps, float* out, void* workspace,
+                              size_t workspace_bytes, bool knots_only, cudaStream_t st) {
   if (!x || !out || rows <= 0 || row_stride < length) return EEGSPEC_EINVAL;
   if (out_cols < 4 || (out_cols & 3) || out_cols > (1 << 24)) return EEGSPEC_EUNSUPPORTED;
   if (reinterpret_cast<uintptr_t>(out) & 15) return EEGSPEC_EALIGN;
@@ -701,7 +737,12 @@ int stft_image_launch(const float* x, long long rows, long long length, long lon
   if (rc != EEGSPEC_OK) return rc;
   if ((rc = check_pow2(nperseg)) != EEGSPEC_OK) return rc;
   if (rows > (1LL << 27)) return EEGSPEC_EUNSUPPORTED;
-  const StftLaunchShape s = stft_shape(rows, nperseg, pl, out_cols);
+  StftLaunchShape s = stft_shape(rows, nperseg, pl, out_cols);
+  if (knots_only) {
+    if (s.use_ws || pl.gather || pl.n_frames < 2 || pl.n_frames > (1 << 20)) return EEGSPEC_EUNSUPPORTED;
+    s.split = 1;            // one CTA per row writes the row's knots
+    s.grid = rows;
+  }
   if (s.use_ws) {
     if (!workspace || workspace_bytes < s.ws_per_cta * (size_t)s.grid) return EEGSPEC_EWORKSPACE;
     if (reinterpret_cast<uintptr_t>(workspace) & 15) return EEGSPEC_EALIGN;
@@ -723,6 +764,7 @@ int stft_image_launch(const float* x, long long rows, long long length, long lon
   a.split = s.split;
   a.logmag_only = 0;
   a.use_ws = s.use_ws;
+  a.knots_only = knots_only ? 1 : 0;
   {
     // Row staging (thread-per-frame path): one pass over the slots, 16-byte alignment everywhere,
     // and the padded extended row has to fit the knot array it aliases.

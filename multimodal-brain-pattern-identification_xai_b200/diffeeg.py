@@ -55,3 +55,48 @@ def spectrogram_condition(spectrogram: torch.Tensor, weight: torch.Tensor, bias:
                                                      _ptr(out), _stream_ptr(dev)),
                   "spectrogram_condition")
     return out
+
+
+def stft_condition(signal: torch.Tensor, config, weight: torch.Tensor, bias: torch.Tensor,
+                   out_length: Optional[int] = None, partner: Optional[torch.Tensor] = None,
+                   alpha: float = 0.5) -> torch.Tensor:
+    """``spectrogram_condition(compute_stft(signal, config), weight, bias, T)`` without the image.
+
+    The reference's trainer computes the (B, C, 33, 2000) image (``DiffEEG_train.py:131``) only for the model to sample
+    0.76 % of its transposed convolution (``diffEEG.py:108-110``).  Every pixel of that image is
+    ``sat(value + delta * fraction)`` of two of the row's 64 normalised STFT knots, so the STFT kernel hands over the
+    knots (17 KB per row instead of 264 KB) and the condition kernel evaluates the pixels it needs from them.
+    Bit-identical to the two-call form; ``signal``: (B, C, L) fp32 on the device, ``out_length`` defaults to L."""
+    from .transform import EPS, OUT_COLS, _stft_keys, stft_plan
+
+    _require_cuda()
+    nperseg, noverlap = _stft_keys(config)
+    batch, n_ch, length = signal.shape
+    if not signal.is_cuda:
+        raise ValueError("stft_condition expects a device tensor")
+    x = signal.to(torch.float32).contiguous()
+    dev = x.device
+    w = weight.detach().to(device=dev, dtype=torch.float32).contiguous()
+    b = bias.detach().to(device=dev, dtype=torch.float32).contiguous()
+    if w.dim() != 4 or w.shape[0] != n_ch or tuple(w.shape[2:]) != (3, 3) or b.shape != (w.shape[1],):
+        raise ValueError("weight must be the (C, H2, 3, 3) ConvTranspose2d parameter and bias (H2,)")
+    t_out = int(out_length) if out_length is not None else length
+    out = torch.empty((batch, w.shape[1], t_out), dtype=torch.float32, device=dev)
+    if batch == 0:
+        return out
+    plan = stft_plan(length, nperseg, noverlap)
+    n_freqs, n_frames = plan["n_freqs"], plan["n_frames"]
+    p = nat.CondParams(n_ch, n_freqs, OUT_COLS, int(w.shape[1]), t_out, float(alpha))
+    part = None
+    if partner is not None:
+        part = partner.to(device=dev, dtype=torch.int32).contiguous()
+        if part.shape != (batch,) or int(part.min()) < 0 or int(part.max()) >= batch:
+            raise ValueError("partner must hold one record index per record")
+    with torch.cuda.device(dev):
+        knots = torch.empty((batch, n_ch, n_freqs, n_frames, 2), dtype=torch.float32, device=dev)
+        nat.check(nat.lib.eegspec_stft_knots_f32(_ptr(x), batch * n_ch, length, length, nperseg, noverlap, OUT_COLS, EPS,
+                                                 _ptr(knots), _stream_ptr(dev)), "stft_condition (knots)")
+        nat.check(nat.lib.eegspec_spec_condition_knots_f32(_ptr(knots), n_frames, batch, C.byref(p), _ptr(w), _ptr(b),
+                                                           _ptr(part), _ptr(out), _stream_ptr(dev)),
+                  "stft_condition")
+    return out

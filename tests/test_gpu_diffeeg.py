@@ -78,3 +78,29 @@ def test_feeds_from_compute_stft_and_errors():
         b200spec.spectrogram_condition(img, torch.randn(18, 16, 3, 3), b, 2000)
     with pytest.raises(ValueError):
         b200spec.spectrogram_condition(img, w, b, 2000, partner=torch.tensor([0, 1, 2, 9]))
+
+
+@pytest.mark.parametrize("shape", [(64, 19, 2000), (5, 8, 2000), (3, 19, 10000)])
+def test_stft_condition_without_the_image_is_bit_identical(shape):
+    """compute_stft's kernel hands over its normalised knots and the condition kernel evaluates the pixels it needs
+    from them: the same bits as spectrogram_condition(compute_stft(x)), training-mode mixing and a NaN channel included."""
+    class Cfg:
+        diffEEG_trainer = {"stft_n_fft": 64, "stft_hop_length": 32, "stft_window": "hann"}
+
+    g = torch.Generator(device="cuda").manual_seed(shape[0])
+    x = torch.randn(shape, device="cuda", generator=g).cumsum(-1) * 0.3 + torch.randn(shape, device="cuda", generator=g)
+    x[0, 1] = 0.0                      # a flat channel
+    x[1, 2, 777] = float("nan")        # a poisoned channel: its image rows are NaN
+    w = torch.randn((shape[1], 16, 3, 3), device="cuda", generator=g) * 0.1
+    b = torch.randn((16,), device="cuda", generator=g) * 0.1
+    img = b200spec.compute_stft(x, Cfg)
+    partner = torch.randperm(shape[0], device="cuda", generator=g)
+    for part in (None, partner):
+        want = b200spec.spectrogram_condition(img, w, b, 2000, partner=part)
+        got = b200spec.stft_condition(x, Cfg, w, b, 2000, partner=part)
+        assert got.shape == want.shape == (shape[0], 16, 2000)
+        assert torch.equal(torch.nan_to_num(got, nan=-7.0), torch.nan_to_num(want, nan=-7.0))
+    plain = b200spec.stft_condition(x, Cfg, w, b, 2000)
+    assert torch.isnan(plain[1]).any() and not torch.isnan(plain[0]).any() and not torch.isnan(plain[2]).any()
+    ref = do.spectrogram_condition_oracle(img[2:3].cpu(), w.cpu(), b.cpu(), 2000)
+    assert (plain[2:3].cpu() - ref).abs().max() <= 5e-5

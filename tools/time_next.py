@@ -20,6 +20,12 @@ if "f2" in which:
     w = torch.randn((19, 16, 3, 3), device="cuda") * 0.1; b = torch.zeros(16, device="cuda")
     print("f2 ms/1024:", timed(lambda: b200spec.spectrogram_condition(img, w, b, 2000)))
     del img
+    class Cfg:
+        diffEEG_trainer = {"stft_n_fft": 64, "stft_hop_length": 32, "stft_window": "hann"}
+    for B in (64, 1024):
+        x = torch.randn((B, 19, 2000), device="cuda", generator=g)
+        print(f"f2 fused stft_condition ms/{B}:", timed(lambda: b200spec.stft_condition(x, Cfg, w, b, 2000)),
+              " two calls:", timed(lambda: b200spec.spectrogram_condition(b200spec.compute_stft(x, Cfg), w, b, 2000)))
 if "f4" in which:
     for B in (1024, 4096):
         x = torch.randn((B, 10000, 20), device="cuda", generator=g).cumsum_(1)
