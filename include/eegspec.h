@@ -30,7 +30,8 @@ enum {
   EEGSPEC_EUNSUPPORTED = -3,  /* legal for the reference, not implemented here (no fallback)   */
   EEGSPEC_ESHORT = -4,        /* record shorter than one window / the crop length              */
   EEGSPEC_EWORKSPACE = -5,    /* workspace missing or too small                                */
-  EEGSPEC_EALIGN = -6         /* output pointer / row pitch not 16-byte aligned                */
+  EEGSPEC_EALIGN = -6,        /* output pointer / row pitch not 16-byte aligned                */
+  EEGSPEC_ESTATICLIMIT = -7   /* request exceeds the built-in scratch of a *_static_* entry    */
 };
 
 int eegspec_abi_version(void);
@@ -314,6 +315,20 @@ size_t eegspec_classifier_spec_workspace(int64_t batch, const eegspec_cls_spec_p
  * drops it and resizes the image with scikit-image -- refused). */
 int eegspec_classifier_spec_f32(const float *win, int64_t batch, const eegspec_cls_spec_params *p, float *out,
                                 int32_t *status, void *workspace, size_t workspace_bytes, void *stream);
+
+/* No-allocation variant of eegspec_classifier_spec_f32.  It has NO counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture,
+ * tight serving loops, harnesses that forbid it).  Same inputs, outputs and results as
+ * eegspec_classifier_spec_f32, but the scratch between its four kernels is a device array built into the
+ * library (EEGSPEC_CLS_SPEC_STATIC_BYTES, held by every GPU that loads the library until exit) instead of a
+ * caller workspace, and the call allocates nothing (no cudaMalloc / cudaFree / allocating library routine).
+ * Limit: eegspec_classifier_spec_workspace(batch, p) <= EEGSPEC_CLS_SPEC_STATIC_BYTES, i.e. at most 17 windows
+ * of (400, 300) per call; beyond it the call returns EEGSPEC_ESTATICLIMIT and launches nothing.  Every call
+ * shares the one array: calls that overlap on the GPU (different streams, different threads) race -- serialise
+ * them.  The array keeps the last call's contents; nothing in it needs to start at zero. */
+#define EEGSPEC_CLS_SPEC_STATIC_BYTES (8u << 20)
+int eegspec_classifier_spec_static_f32(const float *win, int64_t batch, const eegspec_cls_spec_params *p, float *out,
+                                       int32_t *status, void *stream);
 
 /* Number of kernel launches issued by this library since load (bench bookkeeping). */
 int64_t eegspec_launch_count(void);

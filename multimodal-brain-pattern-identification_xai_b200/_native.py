@@ -13,7 +13,8 @@ LIB_PATH = os.path.join(_PKG_DIR, "lib", "libeegspec.so")
 MAX_PAIRS = 32
 
 OK = 0
-EINVAL, ENOVERLAP, EUNSUPPORTED, ESHORT, EWORKSPACE, EALIGN = -1, -2, -3, -4, -5, -6
+EINVAL, ENOVERLAP, EUNSUPPORTED, ESHORT, EWORKSPACE, EALIGN, ESTATICLIMIT = -1, -2, -3, -4, -5, -6, -7
+CLS_SPEC_STATIC_BYTES = 8 << 20     # EEGSPEC_CLS_SPEC_STATIC_BYTES
 
 
 class StftPlan(C.Structure):
@@ -119,6 +120,8 @@ SIGNATURES = {
     "eegspec_classifier_spec_workspace": (C.c_size_t, [C.c_int64, C.POINTER(ClsSpecParams)]),
     "eegspec_classifier_spec_f32": (C.c_int, [C.c_void_p, C.c_int64, C.POINTER(ClsSpecParams), C.c_void_p, C.c_void_p,
                                               C.c_void_p, C.c_size_t, C.c_void_p]),
+    "eegspec_classifier_spec_static_f32": (C.c_int, [C.c_void_p, C.c_int64, C.POINTER(ClsSpecParams), C.c_void_p,
+                                                     C.c_void_p, C.c_void_p]),
     "eegspec_stft_knots_f32": (C.c_int, [C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_int, C.c_int, C.c_int64,
                                          C.c_float, C.c_void_p, C.c_void_p]),
     "eegspec_spec_condition_knots_f32": (C.c_int, [C.c_void_p, C.c_int32, C.c_int64, C.POINTER(CondParams), C.c_void_p,

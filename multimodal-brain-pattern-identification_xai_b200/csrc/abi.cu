@@ -113,6 +113,7 @@ const char* eegspec_strerror(int status) {
     case EEGSPEC_ESHORT: return "record shorter than one window / the crop length";
     case EEGSPEC_EWORKSPACE: return "workspace missing or too small";
     case EEGSPEC_EALIGN: return "pointer not 16-byte aligned";
+    case EEGSPEC_ESTATICLIMIT: return "request exceeds the built-in scratch of this no-allocation entry point (use the workspace variant)";
     default: break;
   }
   if (status > 0) return cudaGetErrorString(static_cast<cudaError_t>(status));
@@ -431,6 +432,11 @@ size_t eegspec_classifier_spec_workspace(int64_t batch, const eegspec_cls_spec_p
 int eegspec_classifier_spec_f32(const float* win, int64_t batch, const eegspec_cls_spec_params* p, float* out,
                                 int32_t* status, void* workspace, size_t workspace_bytes, void* stream) {
   return cls_spec_launch(win, batch, p, out, status, workspace, workspace_bytes, static_cast<cudaStream_t>(stream));
+}
+
+int eegspec_classifier_spec_static_f32(const float* win, int64_t batch, const eegspec_cls_spec_params* p, float* out,
+                                       int32_t* status, void* stream) {
+  return cls_spec_static_launch(win, batch, p, out, status, static_cast<cudaStream_t>(stream));
 }
 
 int eegspec_stft_knots_f32(const float* x, int64_t rows, int64_t length, int64_t row_stride, int nperseg, int noverlap,

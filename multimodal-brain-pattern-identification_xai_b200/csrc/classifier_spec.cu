@@ -28,6 +28,8 @@
 #include <math.h>
 #include <string.h>
 
+#include <mutex>
+
 #include "common.cuh"
 #include "internal.h"
 
@@ -311,6 +313,45 @@ int cls_spec_launch(const float* win, long long batch, const eegspec_cls_spec_pa
   cls_spec_planes_kernel<<<dim3(8, (unsigned)batch), 256, 0, st>>>(a);
   count_launch();
   return (int)cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------------------------------
+// No-allocation variant (no counterpart in the reference; added for callers
+// that cannot call cudaMalloc: CUDA graph capture, tight serving loops, harnesses that forbid it).  The scratch the
+// four kernels above pass between them lives in a file-scope device array instead of a caller workspace: every
+// GPU that loads the library holds EEGSPEC_CLS_SPEC_STATIC_BYTES until exit.  All calls share it (it keeps the
+// last call's contents; every byte a call reads it has written first, so nothing needs clearing beyond the status
+// array that cls_spec_launch already resets): calls that overlap on the GPU race.
+static __device__ __align__(256) unsigned char g_cls_spec_static_scratch[EEGSPEC_CLS_SPEC_STATIC_BYTES];
+
+int cls_spec_static_launch(const float* win, long long batch, const eegspec_cls_spec_params* p, float* out, int* status,
+                           cudaStream_t st) {
+  if (!win || !out || !p || batch <= 0) return EEGSPEC_EINVAL;
+  if (p->rows <= 0 || p->cols <= 0) return EEGSPEC_EINVAL;
+  // overflow-safe: a batch whose workspace does not fit in 2^40 bytes is beyond the limit whatever the product says
+  if ((double)p->rows * (double)p->cols * 4.0 * (double)batch > (double)EEGSPEC_CLS_SPEC_STATIC_BYTES)
+    return EEGSPEC_ESTATICLIMIT;
+  if (cls_spec_workspace(batch, p) > (size_t)EEGSPEC_CLS_SPEC_STATIC_BYTES) return EEGSPEC_ESTATICLIMIT;
+  // In host code the array's name is a host-side stand-in, not a device address: ask the runtime for the address
+  // on the CURRENT device, once per device.
+  static std::mutex mu;
+  static void* addr[64] = {};
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return (int)e;
+  if (dev < 0 || dev >= 64) return EEGSPEC_EUNSUPPORTED;
+  void* ptr = nullptr;
+  {
+    std::lock_guard<std::mutex> lock(mu);
+    if (!addr[dev]) {
+      e = cudaGetSymbolAddress(&ptr, g_cls_spec_static_scratch);
+      if (e != cudaSuccess) return (int)e;
+      if (!ptr) return EEGSPEC_EWORKSPACE;
+      addr[dev] = ptr;
+    }
+    ptr = addr[dev];
+  }
+  return cls_spec_launch(win, batch, p, out, status, ptr, (size_t)EEGSPEC_CLS_SPEC_STATIC_BYTES, st);
 }
 
 }  // namespace eegspec

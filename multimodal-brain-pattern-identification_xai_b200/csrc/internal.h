@@ -56,6 +56,8 @@ void cls_spec_params_default(eegspec_cls_spec_params* p);
 size_t cls_spec_workspace(long long batch, const eegspec_cls_spec_params* p);
 int cls_spec_launch(const float* win, long long batch, const eegspec_cls_spec_params* p, float* out, int* status,
                     void* workspace, size_t workspace_bytes, cudaStream_t st);
+int cls_spec_static_launch(const float* win, long long batch, const eegspec_cls_spec_params* p, float* out, int* status,
+                           cudaStream_t st);
 
 int spec_condition_knots_launch(const float* knots, int n_frames, long long batch, const eegspec_cond_params* p,
                                 const float* weight, const float* bias, const int* partner, float* out, cudaStream_t st);
