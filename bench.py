@@ -771,12 +771,12 @@ def leg_next_rows(torch, b200spec, timed, keep, peak, world, args):
     out["f4_process_eeg"] = {
         "what": "CombinedDataset.process_eeg (XAI_Multimodality.py:1148-1164): band-pass 5 -> NaN fill -> 18 differences -> "
                 "band-pass 6 + 4-tap mean + decimate 4 -> z-score -> (1,37,3000); SciPy-exact float64 recurrences "
-                "(20 + 38 per record): FP64-pipe bound, not HBM bound",
+                "(20 + 38 per record, one thread each): bound by the latency of the float64 recurrences, not by HBM",
         "workload": "(1024,10000,20) parquet rows -> (1024,1,37,3000)",
         "value": world * RECORDS * steps / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms / steps,
         "fp64_Gops_per_s": RECORDS * 10000 * (20 * 31 + 38 * 37) / (ms * 1e-3 / steps) / 1e9,
         "roofline": roofline(RECORDS * bytes_e, ms * 1e-3 / steps, peak,
-                             f"classifier_eeg_filter_kernel + classifier_eeg_finish_kernel, {bytes_e} B/record")}
+                             f"classifier_eeg_first / second / finish kernels, {bytes_e} B/record algorithmic")}
     del x
 
     # ---- (f)3: classifier-side spectrogram post-processing

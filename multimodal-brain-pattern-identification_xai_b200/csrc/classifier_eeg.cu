@@ -22,13 +22,17 @@
 // differences BEFORE the second filter like the reference (filter(a) - filter(b) is not filter(a - b) at this
 // conditioning), and cannot cut a row into chunks.  20 first-filter and 38 second-filter recurrences per record,
 // ~2 000 double-precision operations per sample: FP64-pipe bound (64 lanes per SM), not HBM bound.
-//   kernel 1  one warp per record, one pass over time.  Lanes 0..19 = the parquet columns: first filter + NaN
-//             fill (a NaN turns the rest of a filtered row into NaN, so the fill value -- the nanmean of the row --
-//             is the mean of the prefix, known on the spot).  Every lane then owns row `lane` of the 38-row array
-//             (lanes 0..5 also row 32 + lane): channel rows use their own value, difference rows fetch the two
-//             channels by shuffle; second filter, 4-tap mean + decimation, float4 stores into the workspace.
-//   kernel 2  CTA = (record, output row): mean / std in double precision (two passes over L2-resident data, like
+//   kernel 1  thread = (record, parquet column), one pass over time: first filter + NaN fill (a NaN turns the rest
+//             of a filtered row into NaN, so the fill value -- the nanmean of the row -- is the mean of the prefix,
+//             known on the spot); the filled float64 rows go to the workspace.
+//   kernel 2  thread = (record, row of the 38-row array): channel rows read their own value, difference rows
+//             subtract their two channels; second filter, 4-tap mean + decimation, float4 stores into the workspace.
+//   kernel 3  CTA = (record, output row): mean / std in double precision (two passes over L2-resident data, like
 //             NumPy), z-score, zero padding to 3000.
+// Round 2 ran kernels 1 + 2 as ONE warp per record (lanes = columns, then lanes = rows, differences by shuffle):
+// 237 instructions per sample on 1.7 warps per scheduler, with 20 / 32 and 38 / 64 of the lanes busy -- 5.0 ms per
+// 1 024 records, bound by the latency of its own dependent float64 chain.  One thread per recurrence keeps every
+// lane busy and puts 58 independent recurrences per record on the machine instead of one warp.
 #include <math.h>
 #include <string.h>
 
@@ -41,12 +45,13 @@ constexpr int kClsMaxTaps = EEGSPEC_CLS_MAX_TAPS;   // 13
 
 struct ClsFilterArgs {
   const float* x;        // (batch, n, n_ch) time-major
+  double* y1;            // workspace: (batch, n, n_ch) first-filter output after the NaN fill, float64 like the reference's
   float* dec;            // workspace: (batch, n_rows_all, dec_pitch) decimated second-filter output (in-row terms of the 4-tap mean)
   double* head;          // workspace: (batch, n_rows_all, 4) first second-filter outputs of every row (for the wrap)
   int* status;           // (batch) or null: 1 = a filtered row is all NaN (the reference drops it)
-  long long rec_stride, n, n_dec, dec_pitch;
+  long long batch, rec_stride, n, n_dec, dec_pitch;
   int n_ch, n_rows_all;  // n_rows_all = n_ch + n_pairs rows of the reference's stacked array
-  int src_a[64], src_b[64];   // row r: lane of its minuend / subtrahend channel (src_b < 0: a channel row)
+  int src_a[64], src_b[64];   // row r: its minuend / subtrahend channel (src_b < 0: a channel row)
   double b1[kClsMaxTaps], a1[kClsMaxTaps], b2[kClsMaxTaps], a2[kClsMaxTaps];
 };
 
@@ -97,28 +102,27 @@ __device__ __forceinline__ double pw_combine(const double (&r)[8]) {
   return __dadd_rn(__dadd_rn(__dadd_rn(r[0], r[1]), __dadd_rn(r[2], r[3])), __dadd_rn(__dadd_rn(r[4], r[5]), __dadd_rn(r[6], r[7])));
 }
 
-template <int N1, int N2, bool SKIP>
-__global__ void __launch_bounds__(32) classifier_eeg_filter_kernel(const __grid_constant__ ClsFilterArgs a) {
-  const int lane = threadIdx.x;
-  const long long rec = blockIdx.x;
-  const long long n = a.n;
+constexpr int kClsThreads = 64;   // two warps per CTA: 58 recurrences per record spread over as many SM partitions as possible
+
+// First filter: thread = (record, parquet column).  One pass over time: band-pass, NaN fill (a NaN turns the rest of
+// the filtered row into NaN, so the fill value -- the nanmean of the row -- is the mean of the prefix, known on the
+// spot), the filled float64 row goes to y1[rec][t][ch] for the second kernel.
+template <int N1, bool SKIP>
+__global__ void __launch_bounds__(kClsThreads) classifier_eeg_first_kernel(const __grid_constant__ ClsFilterArgs a) {
+  const long long g = (long long)blockIdx.x * kClsThreads + threadIdx.x;
   const int nc = a.n_ch;
-  const bool is_ch = lane < nc;
-  const float* xp = a.x + rec * a.rec_stride + (is_ch ? lane : 0);
-  // rows of this lane: r0 = lane, r1 = 32 + lane (when they exist)
-  const int r0 = lane, r1 = 32 + lane;
-  const bool has0 = r0 < a.n_rows_all, has1 = r1 < a.n_rows_all;
-  const int sa0 = has0 ? a.src_a[r0] : 0, sb0 = has0 ? a.src_b[r0] : -1;
-  const int sa1 = has1 ? a.src_a[r1] : 0, sb1 = has1 ? a.src_b[r1] : -1;
-  const bool any1 = a.n_rows_all > 32;
-  float* dp0 = a.dec + (rec * a.n_rows_all + r0) * a.dec_pitch;
-  float* dp1 = a.dec + (rec * a.n_rows_all + r1) * a.dec_pitch;
-  double z1[kClsMaxTaps - 1], z2a[kClsMaxTaps - 1], z2b[kClsMaxTaps - 1];
+  if (g >= a.batch * nc) return;
+  const long long rec = g / nc;
+  const int ch = (int)(g - rec * nc);
+  const long long n = a.n;
+  const float* xp = a.x + rec * a.rec_stride + ch;
+  double* yp = a.y1 + rec * n * nc + ch;
+  double z1[kClsMaxTaps - 1];
 #pragma unroll
-  for (int i = 0; i < kClsMaxTaps - 1; ++i) z1[i] = z2a[i] = z2b[i] = 0.0;
+  for (int i = 0; i < kClsMaxTaps - 1; ++i) z1[i] = 0.0;
   double fill = 0.0;
   bool filled = false;
-  // pairwise-sum state of this lane's first-filter output (see above)
+  // pairwise-sum state of this thread's first-filter output (see above)
   PairwiseWalk walk;
   walk.depth = 1;
   walk.len[0] = n;
@@ -130,71 +134,73 @@ __global__ void __launch_bounds__(32) classifier_eeg_filter_kernel(const __grid_
 #pragma unroll
   for (int j = 0; j < 8; ++j) pr[j] = 0.0;
 
-  float xn[8];   // the next eight samples are loaded while the current eight run through the recurrences
+  float xn[8];   // the next eight samples are loaded while the current eight run through the recurrence
 #pragma unroll
-  for (int k = 0; k < 8; ++k) xn[k] = (is_ch && k < n) ? __ldg(xp + (long long)k * nc) : 0.f;
-  float4 q0 = make_float4(0.f, 0.f, 0.f, 0.f), q1 = q0;
-  for (long long t0 = 0; t0 < n; t0 += 8) {
+  for (int k = 0; k < 8; ++k) xn[k] = k < n ? __ldg(xp + (long long)k * nc) : 0.f;
+  const float* xq = xp + 8LL * nc;   // the block after the current one
+  for (long long t0 = 0; t0 < n; t0 += 8, xq += 8LL * nc) {
     float xc[8];
+    if (t0 + 16 <= n) {
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      xc[k] = xn[k];
-      const long long t = t0 + 8 + k;
-      xn[k] = (is_ch && t < n) ? __ldg(xp + t * nc) : 0.f;
+      for (int k = 0; k < 8; ++k) { xc[k] = xn[k]; xn[k] = __ldg(xq + (long long)k * nc); }
+    } else {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) { xc[k] = xn[k]; xn[k] = t0 + 8 + k < n ? __ldg(xq + (long long)k * nc) : 0.f; }
     }
     if (!in_rest && walk.leaf_left < 8) {   // uniform: fewer than 8 samples left in the leaf -> the sequential rest
       pres = pw_combine(pr);
       in_rest = true;
     }
-    double acc[2][2] = {{0.0, 0.0}, {0.0, 0.0}};   // [decimated sample of this iteration][row slot]
+    // Fast path (every block of a NaN-free row whose length is a multiple of 8): eight steps, ONE NaN test -- a NaN
+    // output makes the state NaN, so every later output is NaN too and the last one tells.
+    double yv[8];
+    bool have_y = false;
+    if (!filled && !in_rest && t0 + 8 <= n) {
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      if (t0 + k < n) {                       // uniform across the warp
-        double y1 = 0.0;
-        if (is_ch) {
-          if (!filled) {
-            y1 = df2t_step<N1, SKIP>(a.b1, a.a1, z1, (double)xc[k]);
-            if (y1 != y1) {   // the rest of this filtered row is NaN: nanmean = pairwise sum of the prefix / its length
-              filled = true;
-              const long long t = t0 + k;
-              if (t == 0) {
-                if (a.status) a.status[rec] = 1;
-              } else {
-                double cur = in_rest ? pres : pw_combine(pr);
-                int sp = psp;
-                for (int d = walk.depth - 2; d >= 0; --d)     // up the recursion: finished left halves are added
-                  if (walk.right[d]) cur = __dadd_rn(pstack[--sp], cur);
-                fill = cur / (double)t;
-              }
-              y1 = fill;
-            } else if (in_rest) {
-              pres = __dadd_rn(pres, y1);
-            } else {
-              pr[k] = __dadd_rn(pr[k], y1);
-            }
-          } else {
-            y1 = fill;
-          }
+      for (int k = 0; k < 8; ++k) yv[k] = df2t_step<N1, SKIP>(a.b1, a.a1, z1, (double)xc[k]);
+      have_y = true;
+      if (yv[7] == yv[7]) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          pr[k] = __dadd_rn(pr[k], yv[k]);
+          yp[(long long)k * nc] = yv[k];
         }
-        // row inputs: a channel row is the lane's own value, a difference row fetches its two channels
-        const double va0 = __shfl_sync(0xffffffffu, y1, sa0), vb0 = __shfl_sync(0xffffffffu, y1, sb0 < 0 ? 0 : sb0);
-        const double u0 = sb0 < 0 ? va0 : __dsub_rn(va0, vb0);
-        if (has0) {
-          const double y2 = df2t_step<N2, SKIP>(a.b2, a.a2, z2a, u0);
-          if (t0 + k < 3) a.head[(rec * a.n_rows_all + r0) * 4 + t0 + k] = y2;
-          acc[k >> 2][0] = __dadd_rn(acc[k >> 2][0], y2);
-        }
-        if (any1) {                           // uniform
-          const double va1 = __shfl_sync(0xffffffffu, y1, sa1), vb1 = __shfl_sync(0xffffffffu, y1, sb1 < 0 ? 0 : sb1);
-          const double u1 = sb1 < 0 ? va1 : __dsub_rn(va1, vb1);
-          if (has1) {
-            const double y2 = df2t_step<N2, SKIP>(a.b2, a.a2, z2b, u1);
-            if (t0 + k < 3) a.head[(rec * a.n_rows_all + r1) * 4 + t0 + k] = y2;
-            acc[k >> 2][1] = __dadd_rn(acc[k >> 2][1], y2);
-          }
-        }
+        yp += 8LL * nc;
+        goto walk_step;
       }
     }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      if (t0 + k < n) {                       // uniform
+        double y1;
+        if (!filled) {
+          y1 = have_y ? yv[k] : df2t_step<N1, SKIP>(a.b1, a.a1, z1, (double)xc[k]);
+          if (y1 != y1) {   // the rest of this filtered row is NaN: nanmean = pairwise sum of the prefix / its length
+            filled = true;
+            const long long t = t0 + k;
+            if (t == 0) {
+              if (a.status) a.status[rec] = 1;
+            } else {
+              double cur = in_rest ? pres : pw_combine(pr);
+              int sp = psp;
+              for (int d = walk.depth - 2; d >= 0; --d)     // up the recursion: finished left halves are added
+                if (walk.right[d]) cur = __dadd_rn(pstack[--sp], cur);
+              fill = cur / (double)t;
+            }
+            y1 = fill;
+          } else if (in_rest) {
+            pres = __dadd_rn(pres, y1);
+          } else {
+            pr[k] = __dadd_rn(pr[k], y1);
+          }
+        } else {
+          y1 = fill;
+        }
+        yp[(long long)k * nc] = y1;
+      }
+    }
+    yp += 8LL * nc;
+  walk_step:
     // ---- pairwise walk (uniform): these 8 samples (or the row's last few) are consumed
     {
       const long long used = min(8LL, min(walk.leaf_left, n - t0));
@@ -220,20 +226,87 @@ __global__ void __launch_bounds__(32) classifier_eeg_filter_kernel(const __grid_
         walk.descend();
       }
     }
+  }
+}
+
+// Second filter: thread = (record, row of the reference's 38-row stacked array).  A channel row reads its own
+// filled first-filter output, a difference row subtracts its two channels (BEFORE the filter, like the reference);
+// band-pass, 4-tap mean + decimation, float4 stores into the workspace.
+template <int N2, bool SKIP>
+__global__ void __launch_bounds__(kClsThreads) classifier_eeg_second_kernel(const __grid_constant__ ClsFilterArgs a) {
+  const long long g = (long long)blockIdx.x * kClsThreads + threadIdx.x;
+  if (g >= a.batch * a.n_rows_all) return;
+  const long long rec = g / a.n_rows_all;
+  const int r = (int)(g - rec * a.n_rows_all);
+  const long long n = a.n;
+  const int nc = a.n_ch;
+  const int sa = a.src_a[r], sb = a.src_b[r];
+  const bool diff = sb >= 0;
+  const double* pa = a.y1 + rec * n * nc + sa;
+  const double* pb = a.y1 + rec * n * nc + (diff ? sb : sa);
+  float* dp = a.dec + (rec * a.n_rows_all + r) * a.dec_pitch;
+  double* hp = a.head + (rec * a.n_rows_all + r) * 4;
+  double z2[kClsMaxTaps - 1];
+#pragma unroll
+  for (int i = 0; i < kClsMaxTaps - 1; ++i) z2[i] = 0.0;
+
+  // The next eight inputs are loaded while the current eight run through the recurrence; the subtraction of a
+  // difference row waits until the values are used (doing it at load time would stall on the loads right away).
+  double an[8], bn[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    an[k] = k < n ? pa[(long long)k * nc] : 0.0;
+    bn[k] = (diff && k < n) ? pb[(long long)k * nc] : 0.0;
+  }
+  pa += 8LL * nc;
+  pb += 8LL * nc;
+  float4 q = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (long long t0 = 0; t0 < n; t0 += 8, pa += 8LL * nc, pb += 8LL * nc) {
+    double uc[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) uc[k] = diff ? __dsub_rn(an[k], bn[k]) : an[k];
+    if (t0 + 16 <= n) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        an[k] = pa[(long long)k * nc];
+        if (diff) bn[k] = pb[(long long)k * nc];
+      }
+    } else {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const bool in = t0 + 8 + k < n;
+        an[k] = in ? pa[(long long)k * nc] : 0.0;
+        bn[k] = (diff && in) ? pb[(long long)k * nc] : 0.0;
+      }
+    }
+    double acc[2] = {0.0, 0.0};   // the two decimated samples of this iteration
+    if (t0 + 8 <= n) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const double y2 = df2t_step<N2, SKIP>(a.b2, a.a2, z2, uc[k]);
+        if (t0 == 0 && k < 3) hp[k] = y2;
+        acc[k >> 2] = __dadd_rn(acc[k >> 2], y2);
+      }
+    } else {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        if (t0 + k < n) {                       // uniform
+          const double y2 = df2t_step<N2, SKIP>(a.b2, a.a2, z2, uc[k]);
+          if (t0 + k < 3) hp[t0 + k] = y2;
+          acc[k >> 2] = __dadd_rn(acc[k >> 2], y2);
+        }
+      }
+    }
     // decimated samples m = t0 / 4 and m + 1 exist when their first term does (y[:, 0:-1:4]: t < n - 1); terms
-    // beyond the row's end come from the NEXT row of the flattened array and are added by the second kernel
+    // beyond the row's end come from the NEXT row of the flattened array and are added by the finish kernel
     const long long m = t0 >> 2;            // even
     const bool e0 = t0 < n - 1, e1 = t0 + 4 < n - 1;
     if (e0) {
-      const float v00 = (float)(acc[0][0] * 0.25), v01 = (float)(acc[0][1] * 0.25);
-      const float v10 = (float)(acc[1][0] * 0.25), v11 = (float)(acc[1][1] * 0.25);
-      if ((m & 2) == 0) { q0.x = v00; q1.x = v01; q0.y = v10; q1.y = v11; }
-      else { q0.z = v00; q1.z = v01; q0.w = v10; q1.w = v11; }
+      const float v0 = (float)(acc[0] * 0.25), v1 = (float)(acc[1] * 0.25);
+      if ((m & 2) == 0) { q.x = v0; q.y = v1; }
+      else { q.z = v0; q.w = v1; }
       const long long m_last = e1 ? m + 1 : m;
-      if ((m & 2) || m_last == a.n_dec - 1) {
-        if (has0) *reinterpret_cast<float4*>(dp0 + (m & ~3LL)) = q0;
-        if (has1) *reinterpret_cast<float4*>(dp1 + (m & ~3LL)) = q1;
-      }
+      if ((m & 2) || m_last == a.n_dec - 1) *reinterpret_cast<float4*>(dp + (m & ~3LL)) = q;
     }
   }
 }
@@ -321,7 +394,8 @@ size_t cls_eeg_workspace(long long batch, long long length, int n_ch) {
   if (batch <= 0 || length < 2 || n_ch <= 0) return 0;
   const long long pitch = (cls_n_dec(length) + 3) & ~3LL;
   const long long rows = n_ch + EEGSPEC_MAX_PAIRS;      // an upper bound: the pair count is a run-time parameter
-  return (size_t)batch * rows * ((size_t)pitch * sizeof(float) + 4 * sizeof(double));
+  return (size_t)batch * rows * ((size_t)pitch * sizeof(float) + 4 * sizeof(double)) +
+         (size_t)batch * (size_t)length * n_ch * sizeof(double);                     // + the float64 first-filter rows
 }
 
 int cls_eeg_launch(const float* x, long long batch, long long length, int n_ch, long long rec_stride,
@@ -332,7 +406,7 @@ int cls_eeg_launch(const float* x, long long batch, long long length, int n_ch, 
   if (rec_stride < length * n_ch) return EEGSPEC_EINVAL;
   if (p->n_taps1 != 11 || p->n_taps2 != 13) return EEGSPEC_EUNSUPPORTED;   // orders 5 and 6, the reference's
   if (p->n_pairs < 1 || p->n_pairs > EEGSPEC_MAX_PAIRS || p->n_features < 1 || p->n_features > n_ch) return EEGSPEC_EINVAL;
-  if (n_ch > 32) return EEGSPEC_EUNSUPPORTED;                               // one lane per parquet column
+  if (n_ch > 32) return EEGSPEC_EUNSUPPORTED;                               // rows of the stacked array: n_ch + n_pairs <= 64
   if (p->fixed_length < 1) return EEGSPEC_EINVAL;
   if (fabs(p->a1[0] - 1.0) > 1e-12 || fabs(p->a2[0] - 1.0) > 1e-12) return EEGSPEC_EINVAL;
   for (int i = 0; i < p->n_pairs; ++i)
@@ -357,7 +431,9 @@ int cls_eeg_launch(const float* x, long long batch, long long length, int n_ch, 
     f.src_a[r] = r < n_ch ? r : (r < n_rows_all ? p->pair_a[r - n_ch] : 0);
     f.src_b[r] = r < n_ch ? -1 : (r < n_rows_all ? p->pair_b[r - n_ch] : -1);
   }
-  f.head = static_cast<double*>(workspace);                                   // 8-byte data first
+  f.batch = batch;
+  f.y1 = static_cast<double*>(workspace);                                     // 8-byte data first
+  f.head = f.y1 + (size_t)batch * (size_t)length * n_ch;
   f.dec = reinterpret_cast<float*>(f.head + (size_t)batch * n_rows_all * 4);
   f.status = status;
   bool skip = true;
@@ -372,11 +448,17 @@ int cls_eeg_launch(const float* x, long long batch, long long length, int n_ch, 
     const cudaError_t e = cudaMemsetAsync(status, 0, sizeof(int) * (size_t)batch, st);
     if (e != cudaSuccess) return (int)e;
   }
-  if (skip) classifier_eeg_filter_kernel<11, 13, true><<<(unsigned)batch, 32, 0, st>>>(f);
-  else classifier_eeg_filter_kernel<11, 13, false><<<(unsigned)batch, 32, 0, st>>>(f);
+  const unsigned g1 = (unsigned)((batch * n_ch + kClsThreads - 1) / kClsThreads);
+  const unsigned g2 = (unsigned)((batch * n_rows_all + kClsThreads - 1) / kClsThreads);
+  if (skip) classifier_eeg_first_kernel<11, true><<<g1, kClsThreads, 0, st>>>(f);
+  else classifier_eeg_first_kernel<11, false><<<g1, kClsThreads, 0, st>>>(f);
   count_launch();
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return (int)e;
+  if (skip) classifier_eeg_second_kernel<13, true><<<g2, kClsThreads, 0, st>>>(f);
+  else classifier_eeg_second_kernel<13, false><<<g2, kClsThreads, 0, st>>>(f);
+  count_launch();
+  if ((e = cudaGetLastError()) != cudaSuccess) return (int)e;
 
   ClsFinishArgs g;
   g.dec = f.dec;

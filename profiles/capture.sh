@@ -29,7 +29,8 @@ cap stft_diffeeg stft_image_kernel 8
 cap eeg_transform eeg_transform_lane_kernel 3
 cap gather gather_rows_kernel 3
 cap spec_condition spec_condition_kernel 8
-cap cls_eeg_filter classifier_eeg_filter_kernel 2
+cap cls_eeg_first classifier_eeg_first_kernel 2
+cap cls_eeg_second classifier_eeg_second_kernel 2
 cap cls_spec_column cls_spec_column_kernel 2
 cap cls_spec_row cls_spec_row_kernel 2
 ls -la $OUT
