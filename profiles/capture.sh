@@ -28,7 +28,8 @@ cap stft_hms50s stft_image_kernel 3
 cap stft_diffeeg stft_image_kernel 8
 cap eeg_transform eeg_transform_lane_kernel 3
 cap gather gather_rows_kernel 3
-cap spec_condition spec_condition_kernel 8
+cap spec_condition spec_condition_kernel 20        # image path, 1 024 records (launches 18-23 of the next-rows leg)
+cap spec_condition_knots spec_condition_kernel 26  # fused with compute_stft, 1 024 records (launches 24-29)
 cap cls_eeg_first classifier_eeg_first_kernel 2
 cap cls_eeg_second classifier_eeg_second_kernel 2
 cap cls_spec_column cls_spec_column_kernel 2
