@@ -27,8 +27,8 @@
 //             known on the spot); the filled float64 rows go to the workspace.
 //   kernel 2  thread = (record, row of the 38-row array): channel rows read their own value, difference rows
 //             subtract their two channels; second filter, 4-tap mean + decimation, float4 stores into the workspace.
-//   kernel 3  CTA = (record, output row): mean / std in double precision (two passes over L2-resident data, like
-//             NumPy), z-score, zero padding to 3000.
+//   kernel 3  CTA = (record, output row): z-score with the mean / std from the float64 moments kernel 2 leaves per
+//             row (one pass over the decimated rows), zero padding to 3000.
 // Round 2 ran kernels 1 + 2 as ONE warp per record (lanes = columns, then lanes = rows, differences by shuffle):
 // 237 instructions per sample on 1.7 warps per scheduler, with 20 / 32 and 38 / 64 of the lanes busy -- 5.0 ms per
 // 1 024 records, bound by the latency of its own dependent float64 chain.  One thread per recurrence keeps every
@@ -47,7 +47,8 @@ struct ClsFilterArgs {
   const float* x;        // (batch, n, n_ch) time-major
   double* y1;            // workspace: (batch, n, n_ch) first-filter output after the NaN fill, float64 like the reference's
   float* dec;            // workspace: (batch, n_rows_all, dec_pitch) decimated second-filter output (in-row terms of the 4-tap mean)
-  double* head;          // workspace: (batch, n_rows_all, 4) first second-filter outputs of every row (for the wrap)
+  double* head;          // workspace: (batch, n_rows_all, 8): [0..2] first second-filter outputs of the row (for the wrap),
+                         //            [4], [5] sum and sum of squares of its decimated float32 samples
   int* status;           // (batch) or null: 1 = a filtered row is all NaN (the reference drops it)
   long long batch, rec_stride, n, n_dec, dec_pitch;
   int n_ch, n_rows_all;  // n_rows_all = n_ch + n_pairs rows of the reference's stacked array
@@ -102,6 +103,7 @@ __device__ __forceinline__ double pw_combine(const double (&r)[8]) {
   return __dadd_rn(__dadd_rn(__dadd_rn(r[0], r[1]), __dadd_rn(r[2], r[3])), __dadd_rn(__dadd_rn(r[4], r[5]), __dadd_rn(r[6], r[7])));
 }
 
+constexpr int kClsHead = 8;       // doubles per row in the `head` workspace
 constexpr int kClsThreads = 64;   // two warps per CTA: 58 recurrences per record spread over as many SM partitions as possible
 
 // First filter: thread = (record, parquet column).  One pass over time: band-pass, NaN fill (a NaN turns the rest of
@@ -245,7 +247,8 @@ __global__ void __launch_bounds__(kClsThreads) classifier_eeg_second_kernel(cons
   const double* pa = a.y1 + rec * n * nc + sa;
   const double* pb = a.y1 + rec * n * nc + (diff ? sb : sa);
   float* dp = a.dec + (rec * a.n_rows_all + r) * a.dec_pitch;
-  double* hp = a.head + (rec * a.n_rows_all + r) * 4;
+  double* hp = a.head + (rec * a.n_rows_all + r) * kClsHead;
+  double s1 = 0.0, s2 = 0.0;   // moments of the row as the finish kernel will read it (float32 values), for the z-score
   double z2[kClsMaxTaps - 1];
 #pragma unroll
   for (int i = 0; i < kClsMaxTaps - 1; ++i) z2[i] = 0.0;
@@ -303,12 +306,20 @@ __global__ void __launch_bounds__(kClsThreads) classifier_eeg_second_kernel(cons
     const bool e0 = t0 < n - 1, e1 = t0 + 4 < n - 1;
     if (e0) {
       const float v0 = (float)(acc[0] * 0.25), v1 = (float)(acc[1] * 0.25);
+      s1 += (double)v0;
+      s2 = fma((double)v0, (double)v0, s2);
+      if (e1) {
+        s1 += (double)v1;
+        s2 = fma((double)v1, (double)v1, s2);
+      }
       if ((m & 2) == 0) { q.x = v0; q.y = v1; }
       else { q.z = v0; q.w = v1; }
       const long long m_last = e1 ? m + 1 : m;
       if ((m & 2) || m_last == a.n_dec - 1) *reinterpret_cast<float4*>(dp + (m & ~3LL)) = q;
     }
   }
+  hp[4] = s1;
+  hp[5] = s2;
 }
 
 struct ClsFinishArgs {
@@ -320,43 +331,36 @@ struct ClsFinishArgs {
   float eps;
 };
 
-__device__ __forceinline__ double block_sum(double v, double* red) {
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  __syncthreads();
-  if (lane == 0) red[warp] = v;
-  __syncthreads();
-  double s = 0.0;
-  for (int w = 0; w < (int)(blockDim.x >> 5); ++w) s += red[w];
-  return s;
-}
-
 __global__ void __launch_bounds__(256) classifier_eeg_finish_kernel(const ClsFinishArgs a) {
-  __shared__ double red[8];
   // Output row o is row o of the reference's stacked array: rows 0 .. n_feat - 1 are kept, then
   // select_and_map_channels continues at index n_feat (= 19: EKG and the first 17 differences) -- one sequence.
   const int r = blockIdx.x;
   const long long rec = blockIdx.y;
   const float* d = a.dec + (rec * a.n_rows_all + r) * a.dec_pitch;
+  const double* h = a.head + (rec * a.n_rows_all + r) * kClsHead;
   // the 4-tap mean of the last decimated sample may reach past the row's end: np.roll rolled the FLATTENED
   // array, so those terms are the first samples of the next row
   const long long t_last = 4 * (a.n_dec - 1);
   const int spill = (int)(t_last + 4 - a.n);       // 0 .. 2 terms taken from the next row
   double wrap = 0.0;
-  for (int k = 0; k < spill; ++k) wrap += a.head[(rec * a.n_rows_all + r + 1) * 4 + k];
+  for (int k = 0; k < spill; ++k) wrap += h[kClsHead + k];
   wrap *= 0.25;
-  auto value = [&](long long m) { return (double)d[m] + (m == a.n_dec - 1 ? wrap : 0.0); };
-  double s = 0.0;
-  for (long long m = threadIdx.x; m < a.n_dec; m += blockDim.x) s += value(m);
-  const double mean = block_sum(s, red) / (double)a.n_dec;
-  double s2 = 0.0;
-  for (long long m = threadIdx.x; m < a.n_dec; m += blockDim.x) { const double e = value(m) - mean; s2 += e * e; }
-  const double sd = sqrt(block_sum(s2, red) / (double)a.n_dec);
+  // mean and population standard deviation from the moments the second-filter kernel left (float64 sums of the
+  // float32 samples; the wrap only touches the last sample).  NumPy makes two passes; the moments agree with it
+  // to ~1e-13 relative on these rows (zero-mean band-passed signals), far inside the 1e-4 bar on the z-score.
+  const double v_last = (double)d[a.n_dec - 1];
+  const double s1 = h[4] + wrap;
+  const double s2 = h[5] + ((v_last + wrap) * (v_last + wrap) - v_last * v_last);
+  const double mean = s1 / (double)a.n_dec;
+  const double var = s2 / (double)a.n_dec - mean * mean;
+  const double sd = sqrt(var > 0.0 ? var : 0.0);
   const double inv = 1.0 / (sd + (double)a.eps);
   float* op = a.out + (rec * a.n_rows + r) * a.fixed_length;
-  for (int m = threadIdx.x; m < a.fixed_length; m += blockDim.x)
-    op[m] = m < a.n_dec ? (float)((value(m) - mean) * inv) : 0.f;
+  for (int m = threadIdx.x; m < a.fixed_length; m += blockDim.x) {
+    float v = 0.f;
+    if (m < a.n_dec) v = (float)(((double)d[m] + (m == a.n_dec - 1 ? wrap : 0.0) - mean) * inv);
+    op[m] = v;
+  }
 }
 
 // butter(5 / 6, [0.5, 20] / 100, btype='band') of SciPy, the reference's configuration (XAI_Multimodality.py:205,
@@ -394,7 +398,7 @@ size_t cls_eeg_workspace(long long batch, long long length, int n_ch) {
   if (batch <= 0 || length < 2 || n_ch <= 0) return 0;
   const long long pitch = (cls_n_dec(length) + 3) & ~3LL;
   const long long rows = n_ch + EEGSPEC_MAX_PAIRS;      // an upper bound: the pair count is a run-time parameter
-  return (size_t)batch * rows * ((size_t)pitch * sizeof(float) + 4 * sizeof(double)) +
+  return (size_t)batch * rows * ((size_t)pitch * sizeof(float) + kClsHead * sizeof(double)) +
          (size_t)batch * (size_t)length * n_ch * sizeof(double);                     // + the float64 first-filter rows
 }
 
@@ -434,7 +438,7 @@ int cls_eeg_launch(const float* x, long long batch, long long length, int n_ch, 
   f.batch = batch;
   f.y1 = static_cast<double*>(workspace);                                     // 8-byte data first
   f.head = f.y1 + (size_t)batch * (size_t)length * n_ch;
-  f.dec = reinterpret_cast<float*>(f.head + (size_t)batch * n_rows_all * 4);
+  f.dec = reinterpret_cast<float*>(f.head + (size_t)batch * n_rows_all * kClsHead);
   f.status = status;
   bool skip = true;
   for (int i = 0; i < kClsMaxTaps; ++i) {
