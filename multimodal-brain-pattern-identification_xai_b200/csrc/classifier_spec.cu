@@ -83,9 +83,9 @@ __device__ __forceinline__ int reflect_index(int i, int n) {   // scipy.ndimage 
 // thread = (record, column): everything along axis 0 in one thread, straight out of global memory.  A warp covers
 // 32 consecutive columns, so every row access is one coalesced 128-byte line; 300 K threads per 1 024 records give
 // the latency hiding that a shared-memory slab with one recurrence warp per CTA (the first version: 1.5 ms per
-// 1 024 records) could not.  Pass 1: column mean of the NaN-filled values.  Pass 2: forward notch over the odd
-// extension, output to the workspace image.  Pass 3: backward notch over that (in place, descending rows) with the
-// vertical Gaussian running four rows behind it in a register window.
+// 1 024 records) could not.  Pass 1: forward notch over the odd extension of the NaN-filled column, output to the
+// workspace image, column sum on the way.  Pass 2: backward notch over that (in place, descending rows) with the
+// vertical Gaussian running four rows behind it in a register window; the column mean comes off at the end.
 template <int RADIUS>
 __global__ void __launch_bounds__(128) cls_spec_column_kernel(const SpecArgs a) {
   const int c = blockIdx.x * 128 + threadIdx.x;
@@ -100,11 +100,13 @@ __global__ void __launch_bounds__(128) cls_spec_column_kernel(const SpecArgs a) 
     const float v = __ldg(w + r * ld);
     return v == v ? v : __ldg(fill + r);                     // handle_nan
   };
+  // baseline_correction subtracts the column mean BEFORE the filters.  Everything after it is linear with unit DC
+  // gain (filtfilt with steady-state initial conditions over an odd extension maps a constant to itself, the
+  // Gaussian taps sum to 1), so filters(x - mean) = filters(x) - mean: the mean is accumulated during the forward
+  // pass and subtracted from the final column -- one pass over the image less (float64 recurrences: the two orders
+  // agree to ~1e-12 of the column's scale).
   double s = 0.0;
-#pragma unroll 8
-  for (int r = 0; r < n; ++r) s += (double)load(r);
-  const double mean = s / (double)n;                         // baseline_correction
-  auto x_at = [&](int r) { return (double)load(r) - mean; };
+  auto x_at = [&](int r) { return (double)load(r); };
   // scipy.signal.filtfilt(method='pad', padtype='odd', padlen=9)
   const double x_first = x_at(0), x_last = x_at(n - 1);
   const double b0 = a.nb[0], b1 = a.nb[1], b2 = a.nb[2], a1 = a.na[1], a2 = a.na[2];
@@ -118,7 +120,12 @@ __global__ void __launch_bounds__(128) cls_spec_column_kernel(const SpecArgs a) 
   };
   for (int e = 0; e < kSpecPad; ++e) step(2.0 * x_first - x_at(kSpecPad - e));     // left extension: outputs not needed
 #pragma unroll 4
-  for (int r = 0; r < n; ++r) y[r * ld] = (float)step(x_at(r));
+  for (int r = 0; r < n; ++r) {
+    const double x = x_at(r);
+    s += x;
+    y[r * ld] = (float)step(x);
+  }
+  const float mean = (float)(s / (double)n);
   double tail[kSpecPad];                                     // forward outputs over the right extension
 #pragma unroll
   for (int k = 0; k < kSpecPad; ++k) tail[k] = step(2.0 * x_last - x_at(n - 2 - k));
@@ -155,7 +162,7 @@ __global__ void __launch_bounds__(128) cls_spec_column_kernel(const SpecArgs a) 
       float acc = a.g[0] * W[RADIUS];
 #pragma unroll
       for (int k = 1; k <= RADIUS; ++k) acc += a.g[k] * (W[RADIUS - k] + W[RADIUS + k]);
-      y[rc * ld] = acc;                      // row rc was consumed RADIUS steps ago: never read again
+      y[rc * ld] = acc - mean;               // row rc was consumed RADIUS steps ago: never read again
     }
   }
 }
