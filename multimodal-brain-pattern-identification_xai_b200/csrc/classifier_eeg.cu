@@ -104,6 +104,7 @@ __device__ __forceinline__ double pw_combine(const double (&r)[8]) {
 }
 
 constexpr int kClsHead = 8;       // doubles per row in the `head` workspace
+constexpr int kClsAhead = 3;      // blocks of eight samples the first filter's loads run ahead
 constexpr int kClsThreads = 64;   // two warps per CTA: 58 recurrences per record spread over as many SM partitions as possible
 
 // First filter: thread = (record, parquet column).  One pass over time: band-pass, NaN fill (a NaN turns the rest of
@@ -136,18 +137,29 @@ __global__ void __launch_bounds__(kClsThreads) classifier_eeg_first_kernel(const
 #pragma unroll
   for (int j = 0; j < 8; ++j) pr[j] = 0.0;
 
-  float xn[8];   // the next eight samples are loaded while the current eight run through the recurrence
+  // Loads run kClsAhead blocks of eight samples ahead of the recurrence: one block is ~600 cycles of arithmetic for a
+  // lone warp (74 cycles per step, tools/fp64_latency_probe.cu), less than a DRAM round trip -- with one block of
+  // look-ahead the kernel waited for memory on every block (255 cycles per sample, now 160; deeper changes nothing).
+  float xn[kClsAhead][8];
 #pragma unroll
-  for (int k = 0; k < 8; ++k) xn[k] = k < n ? __ldg(xp + (long long)k * nc) : 0.f;
-  const float* xq = xp + 8LL * nc;   // the block after the current one
+  for (int d = 0; d < kClsAhead; ++d)
+#pragma unroll
+    for (int k = 0; k < 8; ++k) xn[d][k] = 8 * d + k < n ? __ldg(xp + (long long)(8 * d + k) * nc) : 0.f;
+  const float* xq = xp + 8LL * kClsAhead * nc;   // the block kClsAhead after the current one
   for (long long t0 = 0; t0 < n; t0 += 8, xq += 8LL * nc) {
     float xc[8];
-    if (t0 + 16 <= n) {
 #pragma unroll
-      for (int k = 0; k < 8; ++k) { xc[k] = xn[k]; xn[k] = __ldg(xq + (long long)k * nc); }
+    for (int k = 0; k < 8; ++k) {
+      xc[k] = xn[0][k];
+#pragma unroll
+      for (int d = 0; d + 1 < kClsAhead; ++d) xn[d][k] = xn[d + 1][k];
+    }
+    if (t0 + 8 * (kClsAhead + 1) <= n) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) xn[kClsAhead - 1][k] = __ldg(xq + (long long)k * nc);
     } else {
 #pragma unroll
-      for (int k = 0; k < 8; ++k) { xc[k] = xn[k]; xn[k] = t0 + 8 + k < n ? __ldg(xq + (long long)k * nc) : 0.f; }
+      for (int k = 0; k < 8; ++k) xn[kClsAhead - 1][k] = t0 + 8 * kClsAhead + k < n ? __ldg(xq + (long long)k * nc) : 0.f;
     }
     if (!in_rest && walk.leaf_left < 8) {   // uniform: fewer than 8 samples left in the leaf -> the sequential rest
       pres = pw_combine(pr);
