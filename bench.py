@@ -568,7 +568,7 @@ def main():
         result["e2e"] = {"value": world * RECORDS * e2e_steps / e2e_s, "unit": UNIT,
                          "h2d_bytes_per_step": h2d_b.value, "d2h_bytes_per_step": d2h_b.value,
                          "steps": e2e_steps,
-                         "link_GBps_both_directions": (h2d_b.value + d2h_b.value) * e2e_steps / e2e_s / 1e9,
+                         "link_GBps_both_directions": world * (h2d_b.value + d2h_b.value) * e2e_steps / e2e_s / 1e9,
                          "what": "b200spec.eeg_to_spectrogram(pinned host tensor) -> pinned host tensor; "
                                  "H2D (the electrode rows the montage reads), kernels and D2H pipelined in 64-record chunks "
                                  "inside the C ABI call"}
