@@ -498,7 +498,8 @@ def main():
             "mode_r": {"workload": "(1,20,720000) -> (1,20,33,2000): 22 501 frames per row, decimating lerp; L2 flushed",
                        "value": world * 10 / (ms_hr * 1e-3), "unit": UNIT, "ms_per_step": ms_hr / 10,
                        "roofline": roofline(bytes_hr, ms_hr * 1e-3 / 10, peak,
-                                            "stft_image_kernel (gather plan), 20 rows: latency-bound, 20 rows cannot fill 148 SMs")}}
+                                            "stft_long_pixels_kernel + stft_long_normalise_kernel (decimating plan: column chunks, 16 x 20 CTAs), "
+                                            "three launches of ~15 us: launch-latency bound")}}
         del x_h, x_h3
 
     if "cfg3" in legs:

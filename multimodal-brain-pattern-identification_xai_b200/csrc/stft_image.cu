@@ -563,6 +563,126 @@ stft_image_kernel(const StftArgs a) {
   }
 }
 
+// ---------------------------------------------------------------------- decimating plans (very long rows)
+// A 1-hour record (BASELINE configs[3]: 720 000 samples, 22 501 frames) is sampled at 2 000 columns: the plan keeps
+// two frames per column (`gather`), 4 000 slots, which do not fit one CTA's shared memory -- the row kernel above
+// then keeps its knots in a global workspace and every CTA of a row transforms all 4 000 frames (0.5 ms for 20
+// rows, 2 % of the HBM roofline).  Here the COLUMNS are cut into chunks instead: a CTA transforms the frames of
+// its 128 columns (thread = slot), writes the un-normalised pixels and folds their minima / maxima into the
+// row's (row, frequency) slots with atomics (min / max commute: deterministic); a second small kernel
+// normalises in place.  Same arithmetic per pixel as the row kernel up to the order of the normalisation:
+// fma(s1 - s0, fraction, s0), then (v - lo) / (hi - lo + eps), saturated; a NaN anywhere in a frequency row
+// makes the whole row NaN like torch.min / max.
+constexpr int kLongCols = 128;   // columns per CTA (two slots each)
+
+__device__ __forceinline__ unsigned int f2ord(float f) {
+  const unsigned int b = __float_as_uint(f);
+  return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+__device__ __forceinline__ float ord2f(unsigned int u) {
+  return __uint_as_float((u & 0x80000000u) ? (u ^ 0x80000000u) : ~u);
+}
+
+// mm: (rows, F, 4) {ordered min, ordered max, NaN flag, unused}, preset to {0xffffffff, 0, 0, 0}
+template <int LOG2N>
+__global__ void __launch_bounds__(2 * kLongCols) stft_long_pixels_kernel(const StftArgs a, unsigned int* __restrict__ mm) {
+  constexpr int N = 1 << LOG2N, F = N / 2 + 1, PITCH = 2 * kLongCols + 1;
+  __shared__ float S[F * PITCH];
+  const int tid = threadIdx.x, lane = tid & 31;
+  const long long row = blockIdx.y;
+  const int j0 = blockIdx.x * kLongCols;
+  const float* __restrict__ xrow = a.x + row * a.row_stride;
+  {
+    const int j = j0 + (tid >> 1);
+    float v[N];
+    if (j < a.out_cols) {
+      frame_fetch<LOG2N>(a, xrow, 2 * j + (tid & 1), v);
+      frame_fft_mag<LOG2N>(v, [&](int k, float mag) { S[k * PITCH + tid] = log1p_pos(mag); });
+    }
+  }
+  __syncthreads();
+  const int jl = tid & (kLongCols - 1), half = tid >> 7;   // thread = (column, every second frequency row)
+  const int j = j0 + jl;
+  const bool live = j < a.out_cols;
+  float fr = 0.f;
+  if (live) {
+    long long i;
+    int rem;
+    bracket_of(a, j, i, rem);
+    fr = (float)rem * a.inv_d;
+  }
+  float* o = a.out + row * (long long)F * a.out_cols + j;
+  for (int k = half; k < F; k += 2) {
+    float v = 0.f;
+    bool nan = false;
+    float lo = __int_as_float(0x7f800000), hi = __int_as_float(0xff800000);
+    if (live) {
+      const float s0 = S[k * PITCH + 2 * jl], s1 = S[k * PITCH + 2 * jl + 1];
+      v = fmaf(s1 - s0, fr, s0);
+      o[(long long)k * a.out_cols] = v;
+      nan = v != v;
+      if (!nan) lo = hi = v;
+    }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+      lo = fminf(lo, __shfl_xor_sync(0xffffffffu, lo, d));
+      hi = fmaxf(hi, __shfl_xor_sync(0xffffffffu, hi, d));
+    }
+    const bool any_nan = __any_sync(0xffffffffu, nan);
+    if (lane == 0) {
+      unsigned int* m = mm + (row * F + k) * 4;
+      if (lo <= hi) {
+        atomicMin(m, f2ord(lo));
+        atomicMax(m + 1, f2ord(hi));
+      }
+      if (any_nan) atomicOr(m + 2, 1u);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256) stft_long_normalise_kernel(float* __restrict__ out, const unsigned int* __restrict__ mm,
+                                                                  int out_cols, float eps) {
+  const long long rf = blockIdx.y;                       // row * F + frequency
+  const unsigned int* m = mm + rf * 4;
+  const float lo = ord2f(m[0]), hi = ord2f(m[1]);
+  const float inv = 1.0f / (hi - lo + eps);
+  const bool bad = m[2] != 0u || !(inv == inv);
+  float4* o = reinterpret_cast<float4*>(out + rf * out_cols);
+  for (int q = blockIdx.x * 256 + threadIdx.x; 4 * q < out_cols; q += gridDim.x * 256) {
+    float4 v = o[q];
+    if (bad) {
+      v.x = v.y = v.z = v.w = __int_as_float(0x7fc00000);
+    } else {
+      v.x = __saturatef((v.x - lo) * inv); v.y = __saturatef((v.y - lo) * inv);
+      v.z = __saturatef((v.z - lo) * inv); v.w = __saturatef((v.w - lo) * inv);
+    }
+    o[q] = v;
+  }
+}
+
+__global__ void stft_long_preset_kernel(unsigned int* mm, long long n) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) reinterpret_cast<uint4*>(mm)[i] = make_uint4(0xffffffffu, 0u, 0u, 0u);
+}
+
+template <int LOG2N>
+static int stft_long_launch(const StftArgs& a, void* workspace, cudaStream_t st) {
+  constexpr int F = (1 << LOG2N) / 2 + 1;
+  unsigned int* mm = static_cast<unsigned int*>(workspace);
+  const long long n = a.rows * F;
+  stft_long_preset_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(mm, n);
+  count_launch();
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return (int)e;
+  stft_long_pixels_kernel<LOG2N><<<dim3((unsigned)((a.out_cols + kLongCols - 1) / kLongCols), (unsigned)a.rows), 2 * kLongCols, 0, st>>>(a, mm);
+  count_launch();
+  if ((e = cudaGetLastError()) != cudaSuccess) return (int)e;
+  const int gx = (a.out_cols / 4 + 255) / 256;
+  stft_long_normalise_kernel<<<dim3((unsigned)(gx < 1 ? 1 : gx), (unsigned)n), 256, 0, st>>>(a.out, mm, a.out_cols, a.eps);
+  count_launch();
+  return (int)cudaGetLastError();
+}
+
 // ------------------------------------------------------------------------------------- host
 static size_t stft_fixed_smem(int nperseg, int threads, long long n_ends) {
   const int N = nperseg, P = N / 2, F = P + 1;
@@ -786,6 +906,14 @@ static int stft_launch_common(const float* x, long long rows, long long length, 
   a.small_index = ((double)out_cols * (double)pl.n_frames < 4.0e9) ? 1 : 0;
   a.inv_d = 1.0f / (float)a.D;
   a.eps = eps;
+  // decimating plans on the thread-per-frame FFT: columns cut into chunks (stft_long_*), the workspace the row kernel
+  // would have needed (checked above) holds the (row, frequency) minima / maxima
+  if (pl.gather && s.use_ws && !knots_only && rows <= 65535 && rows * pl.n_freqs <= 65535 &&
+      workspace_bytes >= (size_t)rows * pl.n_freqs * 16) {
+    if (nperseg == 64) return stft_long_launch<6>(a, workspace, st);
+    if (nperseg == 32) return stft_long_launch<5>(a, workspace, st);
+    if (nperseg == 16) return stft_long_launch<4>(a, workspace, st);
+  }
   return dispatch(nperseg, a, s.grid, s.smem, s.threads, st);
 }
 

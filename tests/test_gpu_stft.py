@@ -89,6 +89,23 @@ def test_long_continuous_record_config4():
     assert err <= ATOL, f"max abs err {err:.3e}"
 
 
+def test_long_record_column_chunks_nan_rows_and_determinism():
+    """Decimating plans run as column chunks with atomics for the row extrema: a NaN sample poisons exactly the
+    frequency rows it reaches (all of them here: a NaN channel), other channels are untouched, results repeat."""
+    rng = np.random.default_rng(41)
+    x = eeg_like(rng, (2, 3, 300000), walk=0.05)                 # 9 376 frames > 2 x 2000 + 2: the decimating plan
+    assert b200spec.stft_plan(300000, 64, 32)["gather"] == 1
+    x[1, 2, 123456] = np.nan
+    want = so.compute_stft_port(x, Cfg())
+    got = run(x)
+    assert np.isnan(got[1, 2]).any()
+    np.testing.assert_array_equal(np.isnan(got), np.isnan(want))
+    ok = ~np.isnan(want)
+    assert np.abs(got[ok] - want[ok]).max() <= ATOL
+    assert np.array_equal(run(x), got, equal_nan=True)
+    assert got[ok].min() >= 0.0 and got[ok].max() <= 1.0
+
+
 def test_all_nan_channel_and_inf_free_rows():
     x = eeg_like(np.random.default_rng(5), (1, 3, 2000))
     x[0, 1] = np.nan
